@@ -1,0 +1,150 @@
+// clock.cu — KVClientTable::Clock, the progress tracker, the BSP clock edge and the
+// process barrier as device-side flags in peer memory (no server thread, no message).
+//
+// Reference: kClock broadcast to every server thread (worker/kv_client_table.hpp:123-134),
+// ProgressTracker::AdvanceAndGetChangedMinClock (server/util/progress_tracker.cpp:46-72),
+// BSPModel::Clock applying buffered adds then releasing buffered gets
+// (server/consistency/bsp_model.cpp:14-32), Mailbox::Barrier (comm/mailbox.cpp:362-396).
+//
+// Protocol.  Every rank keeps a replica of the progress table in its signal pad; a worker's
+// Clock stores its new clock into slot `worker` of EVERY replica with release.sys, so gates
+// spin on local memory only.  Under BSP the owner of a shard waits for the edge (all
+// workers >= t), folds staging into weights, clears staging and publishes folded[s] = t
+// to every replica; a Get at clock t waits for folded[s] >= t of every shard.
+#include "common.cuh"
+
+namespace mps {
+
+__global__ void __launch_bounds__(256)
+clock_kernel(const __grid_constant__ MpsTableView v, const __grid_constant__ MpsClockView c,
+             int worker, int new_clock, int fold) {
+  // (1) signal.  Kernel boundary ordered this device's earlier pushes; the fence makes them
+  //     visible system-wide before any replica can observe the new clock.
+  if (worker >= 0 && blockIdx.x == 0 && threadIdx.x == 0) {
+    fence_sys();
+    for (int i = 0; i < c.num_ranks; ++i) {
+      const int r = (c.my_rank + i) % c.num_ranks;
+      st_release_sys(c.pad[r] + MPS_PAD_PROGRESS + worker, new_clock);
+    }
+  }
+  if (!fold || c.model != MPS_MODEL_BSP || c.own_count <= 0) return;
+
+  // (2) clock edge: wait until every worker has clocked past new_clock - 1.
+  __shared__ int ok;
+  if (threadIdx.x == 0) ok = spin_until(c, [&] { return pad_min_clock(c) >= new_clock; }) ? 1 : 0;
+  __syncthreads();
+  if (!ok) return;
+
+  // (3) fold my shards: weights += staging; staging = 0 (apply add_buffer_, bsp_model.cpp:20-23)
+  const int64_t tid = static_cast<int64_t>(blockIdx.x) * blockDim.x + threadIdx.x;
+  const int64_t stride = static_cast<int64_t>(gridDim.x) * blockDim.x;
+  for (int s = c.own_first; s < c.own_first + c.own_count; ++s) {
+    if (!v.staging[s]) continue;
+    const int64_t len = static_cast<int64_t>(v.begin[s + 1] - v.begin[s]) * v.vals_per_key;
+    if (v.dtype == MPS_F64) {
+      double* w = static_cast<double*>(v.weights[s]);
+      double* st = static_cast<double*>(v.staging[s]);
+      for (int64_t i = tid; i < len; i += stride) {
+        const double d = st[i];
+        if (d != 0.0) { w[i] += d; st[i] = 0.0; }
+      }
+    } else {
+      float* w = static_cast<float*>(v.weights[s]);
+      float* st = static_cast<float*>(v.staging[s]);
+      const int64_t len4 = len >> 2;
+      for (int64_t i = tid; i < len4; i += stride) {
+        const float4 d = ld_cg_v4(st + 4 * i);
+        if (d.x != 0.f || d.y != 0.f || d.z != 0.f || d.w != 0.f) {
+          float4 x = *reinterpret_cast<float4*>(w + 4 * i);
+          x.x += d.x; x.y += d.y; x.z += d.z; x.w += d.w;
+          *reinterpret_cast<float4*>(w + 4 * i) = x;
+          *reinterpret_cast<float4*>(st + 4 * i) = make_float4(0.f, 0.f, 0.f, 0.f);
+        }
+      }
+      for (int64_t i = (len4 << 2) + tid; i < len; i += stride) {
+        const float d = ld_cg(st + i);
+        if (d != 0.f) { w[i] += d; st[i] = 0.f; }
+      }
+    }
+  }
+
+  // (4) last CTA out publishes folded[s] = new_clock on every replica.
+  __threadfence();
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    int* ctr = c.pad[c.my_rank] + MPS_PAD_LOCALCTR;
+    const int done = atomicAdd(ctr, 1) + 1;
+    if (done == static_cast<int>(gridDim.x)) {
+      *ctr = 0;
+      fence_sys();
+      for (int i = 0; i < c.num_ranks; ++i) {
+        const int r = (c.my_rank + i) % c.num_ranks;
+        for (int s = c.own_first; s < c.own_first + c.own_count; ++s)
+          st_release_sys(c.pad[r] + MPS_PAD_FOLDED + s, new_clock);
+      }
+    }
+  }
+}
+
+__global__ void barrier_kernel(const __grid_constant__ MpsClockView c, int epoch) {
+  if (threadIdx.x != 0 || blockIdx.x != 0) return;
+  fence_sys();
+  for (int i = 0; i < c.num_ranks; ++i) {
+    const int r = (c.my_rank + i) % c.num_ranks;
+    st_release_sys(c.pad[r] + MPS_PAD_BARRIER + c.my_rank, epoch);
+  }
+  const int* bar = c.pad[c.my_rank] + MPS_PAD_BARRIER;
+  spin_until(c, [&] {
+    for (int r = 0; r < c.num_ranks; ++r)
+      if (ld_acquire_sys(bar + r) < epoch) return false;
+    return true;
+  });
+}
+
+__global__ void reset_pad_kernel(const __grid_constant__ MpsClockView c, int start_clock) {
+  int* pad = c.pad[c.my_rank];
+  for (int i = threadIdx.x; i < MPS_MAX_WORKERS; i += blockDim.x) pad[MPS_PAD_PROGRESS + i] = start_clock;
+  for (int i = threadIdx.x; i < MPS_MAX_SHARDS; i += blockDim.x) pad[MPS_PAD_FOLDED + i] = start_clock;
+  if (threadIdx.x == 0) {
+    pad[MPS_PAD_ERROR] = 0;
+    pad[MPS_PAD_MINCLOCK] = start_clock;
+    for (int i = 0; i < 4; ++i) pad[MPS_PAD_LOCALCTR + i] = 0;
+  }
+}
+
+}  // namespace mps
+
+extern "C" {
+
+int mps_clock(const MpsTableView* view, const MpsClockView* clk, int worker, int new_clock, int fold,
+              void* stream) {
+  auto st = static_cast<cudaStream_t>(stream);
+  int grid = 1;
+  if (fold && clk->model == MPS_MODEL_BSP && clk->own_count > 0) {
+    int64_t len = 0;
+    for (int s = clk->own_first; s < clk->own_first + clk->own_count; ++s)
+      len += static_cast<int64_t>(view->begin[s + 1] - view->begin[s]) * view->vals_per_key;
+    int dev = 0, sms = 148;
+    cudaGetDevice(&dev);
+    cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+    int64_t want = (len / 4 + 256 * 4 - 1) / (256 * 4);
+    grid = static_cast<int>(want < 1 ? 1 : (want > sms * 4 ? sms * 4 : want));
+  }
+  mps::clock_kernel<<<grid, 256, 0, st>>>(*view, *clk, worker, new_clock, fold);
+  MPS_LAUNCH_CHECK();
+  return 0;
+}
+
+int mps_barrier(const MpsClockView* clk, int epoch, void* stream) {
+  mps::barrier_kernel<<<1, 32, 0, static_cast<cudaStream_t>(stream)>>>(*clk, epoch);
+  MPS_LAUNCH_CHECK();
+  return 0;
+}
+
+int mps_reset_pad(const MpsClockView* clk, int start_clock, void* stream) {
+  mps::reset_pad_kernel<<<1, 256, 0, static_cast<cudaStream_t>(stream)>>>(*clk, start_clock);
+  MPS_LAUNCH_CHECK();
+  return 0;
+}
+
+}  // extern "C"

@@ -1,0 +1,158 @@
+/*
+ * minips_kernels.h — C ABI of libminips_kernels.so (hand-written sm_100a CUDA).
+ *
+ * Every entry point takes raw device pointers and a cudaStream_t (as void*), enqueues
+ * work on that stream and returns a cudaError_t-compatible int (0 = success) unless
+ * stated otherwise.  Python binds these through ctypes (minips_b200/ops/_lib.py); C++
+ * callers include this header directly.
+ *
+ * "Reference" citations are file:line in the MiniPs reference tree and name the
+ * behaviour an entry point reproduces (the reference itself has no device code).
+ */
+#ifndef MINIPS_KERNELS_H_
+#define MINIPS_KERNELS_H_
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define MPS_MAX_SHARDS 64   /* server shards per table (8 GPUs x up to 8 servers per node) */
+#define MPS_MAX_RANKS 16    /* GPUs (processes) in one NVLink domain */
+#define MPS_MAX_WORKERS 256 /* user workers per task */
+
+/* Signal-pad layout (int32 slots) inside each rank's symmetric pad, one pad per table. */
+#define MPS_PAD_PROGRESS 0                                   /* [MPS_MAX_WORKERS] worker clocks   */
+#define MPS_PAD_FOLDED (MPS_PAD_PROGRESS + MPS_MAX_WORKERS)  /* [MPS_MAX_SHARDS]  BSP fold clocks */
+#define MPS_PAD_BARRIER (MPS_PAD_FOLDED + MPS_MAX_SHARDS)    /* [MPS_MAX_RANKS]   barrier epochs  */
+#define MPS_PAD_ERROR (MPS_PAD_BARRIER + MPS_MAX_RANKS)      /* [1] sticky error (timeout) flag   */
+#define MPS_PAD_MINCLOCK (MPS_PAD_ERROR + 1)                 /* [1] last min clock seen (debug)   */
+#define MPS_PAD_LOCALCTR (MPS_PAD_MINCLOCK + 1)              /* [4] local CTA-completion counters */
+#define MPS_PAD_INTS 512                                     /* pad size in int32 (2 KiB)         */
+
+enum { MPS_MODEL_SSP = 0, MPS_MODEL_BSP = 1, MPS_MODEL_ASP = 2 }; /* driver/engine.hpp:25-27 */
+enum { MPS_F32 = 0, MPS_F64 = 1 };
+
+/*
+ * Range-partitioned view of one table as seen from ONE device: the device analogue of
+ * RangePartitionManager (base/range_partition_manager.hpp:16-66).  weights[s] is the
+ * address, valid on the calling device, of shard s's first value (local memory or a
+ * peer mapping obtained through the symmetric heap).  Shard s owns keys
+ * [begin[s], begin[s+1]).  staging[s] is the BSP add buffer (server/consistency/
+ * bsp_model.cpp:34-43 buffers adds until the clock edge); NULL under SSP/ASP where adds
+ * land in place (server/consistency/ssp_model.cpp:54-56).
+ */
+typedef struct MpsTableView {
+  void* weights[MPS_MAX_SHARDS];
+  void* staging[MPS_MAX_SHARDS];
+  uint32_t begin[MPS_MAX_SHARDS + 1];
+  int32_t num_shards;
+  uint32_t uniform_width; /* >0: every shard but the last has this many keys (owner = key / width) */
+  int32_t vals_per_key;   /* values_ratio of base/range_partition_manager.hpp:47 (k values per key) */
+  int32_t dtype;          /* MPS_F32 / MPS_F64 */
+} MpsTableView;
+
+/*
+ * Device-side progress tracker + consistency gate: ProgressTracker
+ * (server/util/progress_tracker.cpp:46-104) and the BSP/SSP/ASP get-gates
+ * (bsp_model.cpp:45-56, ssp_model.cpp:58-85) as flags in peer memory.  pad[r] is rank
+ * r's signal pad for this table, mapped on the calling device.
+ */
+typedef struct MpsClockView {
+  int32_t* pad[MPS_MAX_RANKS];
+  int32_t num_ranks;
+  int32_t my_rank;
+  int32_t num_workers;  /* workers registered in the tracker (ResetWorker)               */
+  int32_t num_shards;   /* shards of the table                                           */
+  int32_t own_first;    /* shards owned by this rank: [own_first, own_first + own_count) */
+  int32_t own_count;
+  int32_t model;        /* MPS_MODEL_*                                                   */
+  int32_t staleness;    /* SSP staleness                                                 */
+  int64_t timeout_cycles; /* spin-wait budget (SM clocks); on expiry the pad error flag is set */
+} MpsClockView;
+
+/* ---- runtime / symmetric heap (csrc/kernels/heap.cu) ------------------------------- */
+int mps_device_count(void);
+int mps_set_device(int dev);
+int mps_sm_count(int dev);
+int mps_heap_alloc(size_t bytes, void** out);           /* cudaMalloc + zero fill           */
+int mps_heap_free(void* p);
+int mps_ipc_get_handle(void* p, unsigned char out[64]); /* cudaIpcGetMemHandle              */
+int mps_ipc_open_handle(const unsigned char h[64], void** out);
+int mps_ipc_close_handle(void* p);
+int mps_enable_peer(int peer_dev);                      /* same-process multi-device mapping */
+int mps_memset32_async(void* p, int value, size_t n_ints, void* stream);
+const char* mps_error_string(int err);
+
+/* ---- generic KVClientTable ops (csrc/kernels/push_pull.cu) ------------------------- */
+/* Get (worker/kv_client_table.hpp:175-195): vals[i*k + j] = shard(owner(keys[i]))[...].
+ * keys sorted ascending is NOT required on device (routing is per key); out-of-range
+ * keys read as 0 / are dropped on push (range_partition_manager.hpp:24-41 drops them).
+ * If clk != NULL the kernel first gates on the consistency model for `worker` at clock
+ * `progress` (spins on the local pad; no host round trip). */
+int mps_pull(const MpsTableView* view, const MpsClockView* clk, int worker, int progress,
+             const uint32_t* keys, void* vals, int64_t n, void* stream);
+/* Add (kv_client_table.hpp:168-173): shard[...] += vals, red.add at the owner's L2. */
+int mps_push(const MpsTableView* view, const uint32_t* keys, const void* vals, int64_t n,
+             void* stream);
+/* Dense full-table pull / push (k-means centroids, LR eval): contiguous slabs moved with
+ * 16-byte peer loads / vector reds.  dst/src hold begin[num_shards]*vals_per_key values. */
+int mps_pull_dense(const MpsTableView* view, const MpsClockView* clk, int worker, int progress,
+                   void* dst, void* stream);
+int mps_push_dense(const MpsTableView* view, void* src, int zero_src, int rot_shard, void* stream);
+
+/* ---- clock / fold / barrier (csrc/kernels/clock.cu) -------------------------------- */
+/* Clock (kv_client_table.hpp:123-134 + progress_tracker.cpp:46-72): publishes
+ * progress[worker] = new_clock on every rank's pad with release.sys semantics (all prior
+ * pushes of this device are visible first).  Under BSP, if this rank owns shards and
+ * `fold` != 0, it then waits until every worker reached new_clock, folds staging into
+ * the weights of its shards and publishes folded[s] = new_clock (bsp_model.cpp:14-32). */
+int mps_clock(const MpsTableView* view, const MpsClockView* clk, int worker, int new_clock,
+              int fold, void* stream);
+/* Device-side barrier over the pads (comm/mailbox.cpp:362-396 semantics). */
+int mps_barrier(const MpsClockView* clk, int epoch, void* stream);
+/* ResetWorker (bsp_model.cpp:70-83): zero progress/folded on the LOCAL pad. */
+int mps_reset_pad(const MpsClockView* clk, int start_clock, void* stream);
+
+/* ---- sparse logistic regression (csrc/kernels/lr.cu) ------------------------------- */
+typedef struct MpsCsr {
+  const int64_t* row_ptr; /* [n_rows + 1] */
+  const uint32_t* col;    /* [nnz] 0-based feature ids (lib/parser.hpp:33) */
+  const float* val;       /* [nnz] */
+  const float* label;     /* [n_rows] in {0,1} (lr_example.cpp:296-297 maps y<0 to 0) */
+  int64_t n_rows;
+} MpsCsr;
+
+/* One LR iteration, sparse regime: Get + forward SpMV + sigmoid + gradient + Add in ONE
+ * kernel (lr_example.cpp:260,293-313): each warp walks a CSR row, loads the row's weights
+ * straight from the owning shards (peer ld), reduces the logit, and issues the per-nnz
+ * red.add of alpha*x*(y-pred) into the owner's staging/weights.  Rows are
+ * [row_begin, row_begin + batch) modulo n_rows (BatchDataSampler wrap-around,
+ * lib/batch_data_sampler.cpp:50-71).  loss_out[0] += sum logloss, loss_out[1] += #correct. */
+int mps_lr_step_sparse(const MpsTableView* view, const MpsClockView* clk, int worker, int progress,
+                       const MpsCsr* csr, int64_t row_begin, int64_t batch, float alpha,
+                       float* loss_out, void* stream);
+
+/* Dense regime, persistent cooperative kernel running `n_iters` whole iterations
+ * (Get -> SpMV -> grad -> Add -> Clock [-> BSP fold]) without returning to the host:
+ * slab-pull of all shards into `replica`, row pass accumulating into `gacc` (both scratch,
+ * begin[num_shards] floats, gacc zero on entry and on exit), slab-push with vector reds,
+ * then the clock / fold protocol of mps_clock.  batch_starts[i] is the first row of
+ * iteration i; loss_out[2*i], loss_out[2*i+1] as above.  start_clock is the worker's clock
+ * before the first iteration. */
+int mps_lr_train_dense(const MpsTableView* view, const MpsClockView* clk, int worker,
+                       int start_clock, const MpsCsr* csr, const int64_t* batch_starts,
+                       int n_iters, int64_t batch, float alpha, float* replica, float* gacc,
+                       float* loss_out, int max_ctas, void* stream);
+
+/* Accuracy / logloss of local rows against a local full copy of the weights
+ * (lr_example.cpp:61-87).  out[0] += logloss, out[1] += #correct. */
+int mps_lr_eval(const float* weights, const MpsCsr* csr, int64_t row_begin, int64_t n,
+                float* out, void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* MINIPS_KERNELS_H_ */

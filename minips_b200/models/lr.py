@@ -1,0 +1,216 @@
+"""Sparse logistic regression on the parameter server (reference apps/logistic_regression/
+lr_example.cpp:97-385): mini-batch SGD where every iteration is Get(batch keys) -> forward ->
+gradient -> Add -> Clock.  The device implementation runs those as phases of one fused
+kernel (csrc/kernels/lr.cu); this module holds the data container, the synthetic libsvm-shaped
+generator that replaces the HDFS loader, the trainer and a plain PyTorch fp32 oracle.
+"""
+from __future__ import annotations
+
+import ctypes as C
+from dataclasses import dataclass
+from typing import List, Optional, Tuple
+
+import torch
+
+from ..ops import _lib
+from ..parallel.device_table import DeviceTable, KVClientTable
+from ..parallel.types import ModelType
+
+
+@dataclass
+class CsrBatchSource:
+    """Local samples of one node in CSR form (labels in {0,1}; reference maps y<0 to 0,
+    lr_example.cpp:296-297; feature ids 0-based, lib/parser.hpp:33)."""
+    row_ptr: torch.Tensor  # int64 [n+1]
+    col: torch.Tensor      # int32 [nnz] (uint32 bit patterns)
+    val: torch.Tensor      # float32 [nnz]
+    label: torch.Tensor    # float32 [n]
+
+    @property
+    def n_rows(self) -> int:
+        return self.label.numel()
+
+    @property
+    def nnz(self) -> int:
+        return self.col.numel()
+
+    def to(self, device) -> "CsrBatchSource":
+        return CsrBatchSource(self.row_ptr.to(device), self.col.to(device), self.val.to(device),
+                              self.label.to(device))
+
+    def pin(self) -> "CsrBatchSource":
+        return CsrBatchSource(self.row_ptr.pin_memory(), self.col.pin_memory(), self.val.pin_memory(),
+                              self.label.pin_memory())
+
+    def c_struct(self) -> _lib.Csr:
+        m = _lib.Csr()
+        m.row_ptr = self.row_ptr.data_ptr()
+        m.col = self.col.data_ptr()
+        m.val = self.val.data_ptr()
+        m.label = self.label.data_ptr()
+        m.n_rows = self.n_rows
+        return m
+
+    def rows(self, start: int, count: int) -> "CsrBatchSource":
+        """Contiguous row slice [start, start+count) (no wrap) re-based to its own row_ptr."""
+        rp = self.row_ptr[start:start + count + 1]
+        b, e = int(rp[0]), int(rp[-1])
+        return CsrBatchSource(rp - rp[0], self.col[b:e], self.val[b:e], self.label[start:start + count])
+
+
+def make_synthetic(n_rows: int, n_features: int, nnz_per_row: int = 40, device="cuda", seed: int = 0,
+                   binary_values: bool = False, chunk_rows: int = 1 << 20) -> CsrBatchSource:
+    """libsvm-shaped synthetic data generated directly in device memory: uniform feature ids,
+    N(0,1) values, labels drawn from a hidden linear model."""
+    g = torch.Generator(device=device)
+    g.manual_seed(seed)
+    w_true = torch.randn(n_features, device=device, generator=torch.Generator(device=device).manual_seed(12345))
+    col = torch.empty(n_rows * nnz_per_row, dtype=torch.int32, device=device)
+    val = torch.empty(n_rows * nnz_per_row, dtype=torch.float32, device=device)
+    label = torch.empty(n_rows, dtype=torch.float32, device=device)
+    for r0 in range(0, n_rows, chunk_rows):
+        n = min(chunk_rows, n_rows - r0)
+        c = torch.randint(0, n_features, (n, nnz_per_row), device=device, generator=g, dtype=torch.int64)
+        c, _ = torch.sort(c, dim=1)
+        v = torch.ones(n, nnz_per_row, device=device) if binary_values else \
+            torch.randn(n, nnz_per_row, device=device, generator=g)
+        z = (w_true[c] * v).sum(1) * (4.0 / nnz_per_row ** 0.5)
+        y = (torch.rand(n, device=device, generator=g) < torch.sigmoid(z)).float()
+        col[r0 * nnz_per_row:(r0 + n) * nnz_per_row] = c.reshape(-1).to(torch.int32)
+        val[r0 * nnz_per_row:(r0 + n) * nnz_per_row] = v.reshape(-1)
+        label[r0:r0 + n] = y
+    row_ptr = torch.arange(0, (n_rows + 1) * nnz_per_row, nnz_per_row, dtype=torch.int64, device=device)
+    return CsrBatchSource(row_ptr, col, val, label)
+
+
+class SparseLRTrainer:
+    """Device trainer bound to one worker's KVClientTable."""
+
+    def __init__(self, client: KVClientTable, data: CsrBatchSource, alpha: float = 0.1):
+        self.client = client
+        self.table: DeviceTable = client.table
+        self.data = data
+        self.alpha = float(alpha)
+        self.lib = client.lib
+        self.dev = client.dev
+        self._replica: Optional[torch.Tensor] = None
+        self._gacc: Optional[torch.Tensor] = None
+        assert self.table.dtype == torch.float32 and self.table.k == 1
+
+    def _scratch(self):
+        if self._replica is None:
+            n = self.table.num_keys
+            self._replica = torch.empty(n, dtype=torch.float32, device=self.dev)
+            self._gacc = torch.zeros(n, dtype=torch.float32, device=self.dev)
+        return self._replica, self._gacc
+
+    def dense_regime(self, batch: int) -> bool:
+        """Slab pull/push pays off once the batch touches a good part of the table."""
+        nnz_per_row = max(1, self.data.nnz // max(1, self.data.n_rows))
+        return batch * nnz_per_row * 4 >= self.table.num_keys
+
+    def train_dense(self, batch_starts: torch.Tensor, batch: int, max_ctas: int = 0,
+                    csr: Optional[_lib.Csr] = None, loss: Optional[torch.Tensor] = None) -> torch.Tensor:
+        """Run len(batch_starts) iterations inside one persistent kernel.  Returns the per-
+        iteration (logloss sum, #correct) tensor [n_iters, 2] (device, async)."""
+        c = self.client
+        t = self.table
+        n_iters = int(batch_starts.numel())
+        replica, gacc = self._scratch()
+        if loss is None:
+            loss = torch.zeros(n_iters, 2, dtype=torch.float32, device=self.dev)
+        cv = t.clock_view()
+        if csr is None:
+            csr = self.data.c_struct()
+        c._local_gate()
+        _lib.check(self.lib.mps_lr_train_dense(
+            C.byref(t.view), C.byref(cv), c.worker_id, c.progress, C.byref(csr),
+            C.c_void_p(batch_starts.data_ptr()), n_iters, batch, self.alpha,
+            C.c_void_p(replica.data_ptr()), C.c_void_p(gacc.data_ptr()), C.c_void_p(loss.data_ptr()),
+            max_ctas, c._sp()), "lr_train_dense")
+        # host mirror of the clock (the kernel published the device-side one)
+        with t.lock:
+            c.progress += n_iters
+            t.local_clock[c.worker_id] = c.progress
+            ev = torch.cuda.Event()
+            ev.record(c.stream or torch.cuda.current_stream())
+            t.local_events[c.worker_id] = ev
+            t.fold_clock = c.progress
+            t.lock.notify_all()
+        return loss
+
+    def train_stream(self, loader, row_starts, host_loss: Optional[torch.Tensor] = None) -> torch.Tensor:
+        """End-to-end iterations: every step copies its batch from pinned host memory (double
+        buffered on a copy stream), trains on it, and returns its (logloss, #correct) to a
+        pinned host tensor.  Returns that [n_steps, 2] host tensor (valid after a sync)."""
+        n = len(row_starts)
+        batch = loader.batch
+        if host_loss is None:
+            host_loss = torch.zeros(n, 2, dtype=torch.float32).pin_memory()
+        dev_loss = torch.zeros(n, 2, dtype=torch.float32, device=self.dev)
+        zero_start = torch.zeros(1, dtype=torch.int64, device=self.dev)
+        stream = self.client.stream or torch.cuda.current_stream()
+        pending = loader.prefetch(int(row_starts[0]))
+        for i in range(n):
+            k = pending
+            if i + 1 < n:
+                pending = loader.prefetch(int(row_starts[i + 1]))
+            loader.acquire(k, stream)
+            self.train_dense(zero_start, batch, csr=loader.staged_struct(k), loss=dev_loss[i:i + 1])
+            loader.release(k, stream)
+            host_loss[i].copy_(dev_loss[i], non_blocking=True)
+        return host_loss
+
+    def step_sparse(self, row_begin: int, batch: int, loss: Optional[torch.Tensor] = None) -> torch.Tensor:
+        """One iteration in the sparse regime: fused pull+forward+grad+push kernel, then Clock."""
+        c = self.client
+        t = self.table
+        if loss is None:
+            loss = torch.zeros(2, dtype=torch.float32, device=self.dev)
+        cv = t.clock_view()
+        csr = self.data.c_struct()
+        c._local_gate()
+        _lib.check(self.lib.mps_lr_step_sparse(
+            C.byref(t.view), C.byref(cv), c.worker_id, c.progress, C.byref(csr), row_begin, batch,
+            self.alpha, C.c_void_p(loss.data_ptr()), c._sp()), "lr_step_sparse")
+        c.clock()
+        return loss
+
+    def evaluate(self, weights: Optional[torch.Tensor] = None, n: Optional[int] = None) -> Tuple[float, float]:
+        """(mean logloss, accuracy) of the local rows (reference test_error, lr_example.cpp:61-87)."""
+        if weights is None:
+            weights = self.client.get_all()
+        n = self.data.n_rows if n is None else n
+        out = torch.zeros(2, dtype=torch.float32, device=self.dev)
+        csr = self.data.c_struct()
+        _lib.check(self.lib.mps_lr_eval(C.c_void_p(weights.data_ptr()), C.byref(csr), 0, n,
+                                        C.c_void_p(out.data_ptr()), self.client._sp()), "lr_eval")
+        o = out.tolist()
+        return o[0] / n, o[1] / n
+
+
+# ------------------------------------------------------------------ fp32 PyTorch oracle
+def oracle_step(w: torch.Tensor, data: CsrBatchSource, row_begin: int, batch: int, alpha: float
+                ) -> Tuple[torch.Tensor, float, float]:
+    """Gradient of one worker's batch at weights w (textbook mini-batch SGD; the reference's
+    stale-delta accumulation quirk, SURVEY 2.8-2, is deliberately not reproduced).
+    Returns (delta, logloss_sum, n_correct)."""
+    n = data.n_rows
+    idx = (torch.arange(batch, device=w.device) + row_begin) % n
+    rp = data.row_ptr
+    starts, ends = rp[idx], rp[idx + 1]
+    lens = ends - starts
+    row_of = torch.repeat_interleave(torch.arange(batch, device=w.device), lens)
+    offs = torch.arange(int(lens.sum()), device=w.device) - torch.repeat_interleave(
+        torch.cumsum(lens, 0) - lens, lens)
+    nz = torch.repeat_interleave(starts, lens) + offs
+    cols = data.col[nz].to(torch.int64) & 0xFFFFFFFF
+    vals = data.val[nz]
+    z = torch.zeros(batch, dtype=torch.float32, device=w.device).index_add_(0, row_of, w[cols] * vals)
+    y = data.label[idx]
+    pred = torch.sigmoid(z)
+    g = alpha * (y - pred)
+    delta = torch.zeros_like(w).index_add_(0, cols, g[row_of] * vals)
+    loss = (torch.clamp(z, min=0) + torch.log1p(torch.exp(-z.abs())) - y * z).sum().item()
+    correct = ((pred > 0.5) == (y > 0.5)).float().sum().item()
+    return delta, loss, correct

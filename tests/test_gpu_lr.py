@@ -1,0 +1,115 @@
+"""Fused sparse-LR kernels against a plain PyTorch fp32 oracle of the same iteration."""
+import pytest
+import torch
+
+from minips_b200.parallel.types import MLTask, ModelType, Node, WorkerAlloc
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.fixture()
+def engine():
+    from minips_b200.parallel.engine import Engine
+    n = Node(0, "localhost", 0)
+    e = Engine(n, [n], device=0)
+    e.start_everything(num_server_threads_per_node=8)
+    yield e
+    e.stop_everything()
+
+
+def _run(engine, tid, fn, workers=1):
+    task = MLTask()
+    task.set_worker_alloc([WorkerAlloc(0, workers)])
+    task.set_tables([tid])
+    task.set_lambda(fn)
+    engine.run(task)
+
+
+def _oracle(data, num_dims, starts, batch, alpha):
+    from minips_b200.models.lr import oracle_step
+    w = torch.zeros(num_dims, device="cuda")
+    stats = []
+    for s in starts:
+        d, loss, correct = oracle_step(w, data, int(s), batch, alpha)
+        w = w + d
+        stats.append((loss, correct))
+    return w, stats
+
+
+@pytest.mark.parametrize("model", [ModelType.BSP, ModelType.SSP, ModelType.ASP])
+def test_dense_train_matches_oracle(engine, model):
+    from minips_b200.models.lr import SparseLRTrainer, make_synthetic
+    num_dims, n_rows, batch, iters, alpha = 50_001, 20_000, 4096, 6, 0.05
+    data = make_synthetic(n_rows, num_dims, 40, seed=3)
+    tid = engine.create_table(num_dims=num_dims, model_type=model, staleness=2)
+    starts = torch.tensor([0, 4096, 17_000, 19_999, 5, 12_345], dtype=torch.int64, device="cuda")
+    out = {}
+
+    def fn(info):
+        tr = SparseLRTrainer(info.create_kv_client_table(tid), data, alpha)
+        out["loss"] = tr.train_dense(starts, batch)
+        out["w"] = tr.client.get_all()
+        out["gacc_clean"] = bool((tr._gacc == 0).all())
+        out["eval"] = tr.evaluate(out["w"])
+
+    _run(engine, tid, fn)
+    w_ref, stats = _oracle(data, num_dims, starts.tolist(), batch, alpha)
+    torch.testing.assert_close(out["w"], w_ref, rtol=2e-4, atol=2e-5)
+    loss = out["loss"].cpu()
+    for i, (l, c) in enumerate(stats):
+        assert abs(loss[i, 0].item() - l) <= 2e-3 * abs(l) + 1e-2
+        assert abs(loss[i, 1].item() - c) <= 2
+    assert out["gacc_clean"]
+    mean_loss, acc = out["eval"]
+    assert 0.0 < mean_loss < 0.75 and 0.5 <= acc <= 1.0
+
+
+@pytest.mark.parametrize("model", [ModelType.BSP, ModelType.ASP])
+def test_sparse_step_matches_oracle(engine, model):
+    from minips_b200.models.lr import SparseLRTrainer, make_synthetic
+    num_dims, n_rows, batch, alpha = 2_000_003, 6000, 1024, 0.1
+    data = make_synthetic(n_rows, num_dims, 40, seed=5)
+    tid = engine.create_table(num_dims=num_dims, model_type=model)
+    starts = [0, 1024, 5500]
+    out = {}
+
+    def fn(info):
+        tr = SparseLRTrainer(info.create_kv_client_table(tid), data, alpha)
+        losses = [tr.step_sparse(s, batch) for s in starts]
+        out["w"] = tr.client.get_all()
+        out["loss"] = torch.stack(losses).cpu()
+
+    _run(engine, tid, fn)
+    w_ref, stats = _oracle(data, num_dims, starts, batch, alpha)
+    torch.testing.assert_close(out["w"], w_ref, rtol=2e-4, atol=2e-5)
+    for i, (l, c) in enumerate(stats):
+        assert abs(out["loss"][i, 0].item() - l) <= 2e-3 * abs(l) + 1e-2
+
+
+def test_long_rows(engine):
+    """Rows with more than 64 non-zeros take the re-read path of both kernels."""
+    from minips_b200.models.lr import SparseLRTrainer, make_synthetic
+    num_dims, n_rows, batch, alpha = 10_000, 512, 512, 0.01
+    data = make_synthetic(n_rows, num_dims, 150, seed=7)
+    tid_d = engine.create_table(num_dims=num_dims, model_type=ModelType.BSP)
+    tid_s = engine.create_table(num_dims=num_dims, model_type=ModelType.BSP)
+    out = {}
+    starts = torch.zeros(2, dtype=torch.int64, device="cuda")
+
+    def fn(info):
+        a = SparseLRTrainer(info.create_kv_client_table(tid_d), data, alpha)
+        a.train_dense(starts, batch)
+        out["dense"] = a.client.get_all()
+        b = SparseLRTrainer(info.create_kv_client_table(tid_s), data, alpha)
+        b.step_sparse(0, batch)
+        b.step_sparse(0, batch)
+        out["sparse"] = b.client.get_all()
+
+    task = MLTask()
+    task.set_worker_alloc([WorkerAlloc(0, 1)])
+    task.set_tables([tid_d, tid_s])
+    task.set_lambda(fn)
+    engine.run(task)
+    w_ref, _ = _oracle(data, num_dims, [0, 0], batch, alpha)
+    torch.testing.assert_close(out["dense"], w_ref, rtol=3e-4, atol=3e-5)
+    torch.testing.assert_close(out["sparse"], w_ref, rtol=3e-4, atol=3e-5)
