@@ -264,6 +264,8 @@ class KVClientTable:
         new_clock = self.progress + 1
         fold = 0
         s = self.stream or torch.cuda.current_stream()
+        # decide-who-folds, enqueue and publish the host mirror atomically: two local workers
+        # clocking concurrently must not both conclude "the other one is last"
         with t.lock:
             others = [w for w in t.local_workers if w != self.worker_id]
             last_local = all(t.local_clock[w] >= new_clock for w in others)
@@ -272,12 +274,11 @@ class KVClientTable:
                 for w in others:
                     if w in t.local_events:
                         s.wait_event(t.local_events[w])
-        cv = t.clock_view()
-        _lib.check(self.lib.mps_clock(C.byref(t.view), C.byref(cv), self.worker_id, new_clock, fold,
-                                      self._sp()), "clock")
-        ev = torch.cuda.Event()
-        ev.record(s)
-        with t.lock:
+            cv = t.clock_view()
+            _lib.check(self.lib.mps_clock(C.byref(t.view), C.byref(cv), self.worker_id, new_clock, fold,
+                                          self._sp()), "clock")
+            ev = torch.cuda.Event()
+            ev.record(s)
             t.local_clock[self.worker_id] = new_clock
             t.local_events[self.worker_id] = ev
             if fold:
