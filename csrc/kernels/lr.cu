@@ -17,6 +17,9 @@
 //           cooperative kernel so no host round trip gates an iteration.
 #include <cooperative_groups.h>
 
+#include <cstdio>
+#include <mutex>
+
 #include "common.cuh"
 
 namespace cg = cooperative_groups;
@@ -391,3 +394,80 @@ int mps_lr_eval(const float* weights, const MpsCsr* csr, int64_t row_begin, int6
 }
 
 }  // extern "C"
+
+// ------------------------------------------------------------------ allocation-free variant
+// mps_lr_train_dense needs two scratch vectors (the weight replica and the local gradient
+// accumulator) that its caller must allocate.  Some callers cannot: a host that has already
+// handed every free byte of HBM to its own pool so a fresh cudaMalloc fails, code that runs
+// where an allocation's implicit device-wide synchronisation would stall other streams
+// (a latency-critical serving or control loop), or a plain C/C++ embedder that has no
+// allocator of its own to hand us memory from.  For them the scratch below is part of the
+// library image itself: it exists from the moment the module is loaded on a GPU until the
+// process exits, on every GPU that loads it, whether or not the entry point is ever called.
+#define MPS_NOALLOC_SCRATCH_FLOATS (2 * (size_t)MPS_NOALLOC_MAX_KEYS) /* replica | gacc = 8 MiB */
+static __device__ __align__(256) float g_noalloc_scratch[MPS_NOALLOC_SCRATCH_FLOATS];
+
+namespace mps {
+namespace {
+constexpr int kMaxDevices = 64;
+std::mutex g_noalloc_mu;
+float* g_noalloc_ptr[kMaxDevices] = {nullptr};  // device address of g_noalloc_scratch, per device
+
+// In host code `g_noalloc_scratch` is only a handle for the runtime, not an address a kernel
+// can use; the real per-device address has to be asked for, with that device current.
+int noalloc_scratch_for_current_device(float** out) {
+  int dev = 0;
+  MPS_CHECK(cudaGetDevice(&dev));
+  if (dev < 0 || dev >= kMaxDevices) return static_cast<int>(cudaErrorInvalidDevice);
+  std::lock_guard<std::mutex> lk(g_noalloc_mu);
+  if (g_noalloc_ptr[dev] == nullptr) {
+    float* p = nullptr;
+    MPS_CHECK(cudaGetSymbolAddress(reinterpret_cast<void**>(&p), g_noalloc_scratch));
+    if (p == nullptr) return static_cast<int>(cudaErrorInvalidSymbol);
+    g_noalloc_ptr[dev] = p;
+  }
+  *out = g_noalloc_ptr[dev];
+  return 0;
+}
+}  // namespace
+}  // namespace mps
+
+extern "C" int mps_lr_train_dense_noalloc(const MpsTableView* view, const MpsClockView* clk, int worker,
+                                          int start_clock, const MpsCsr* csr, const int64_t* batch_starts,
+                                          int n_iters, int64_t batch, float alpha, float* loss_out,
+                                          int max_ctas, void* stream) {
+  if (n_iters <= 0) return 0;
+  if (view->dtype != MPS_F32 || view->vals_per_key != 1) return static_cast<int>(cudaErrorInvalidValue);
+  const uint64_t n_keys = static_cast<uint64_t>(view->begin[view->num_shards]) - view->begin[0];
+  if (n_keys > MPS_NOALLOC_MAX_KEYS) {
+    fprintf(stderr,
+            "mps_lr_train_dense_noalloc: table has %llu keys but the built-in scratch holds at most %llu "
+            "(MPS_NOALLOC_MAX_KEYS); use mps_lr_train_dense with caller-provided scratch instead\n",
+            static_cast<unsigned long long>(n_keys), static_cast<unsigned long long>(MPS_NOALLOC_MAX_KEYS));
+    return static_cast<int>(cudaErrorInvalidValue);
+  }
+  float* scratch = nullptr;
+  const int rc = mps::noalloc_scratch_for_current_device(&scratch);
+  if (rc != 0) return rc;
+  float* replica = scratch;
+  float* gacc = scratch + MPS_NOALLOC_MAX_KEYS;
+  auto st = static_cast<cudaStream_t>(stream);
+  // The array still holds whatever the previous call left.  The replica is overwritten by the
+  // slab pull before it is read; the gradient accumulator must start at zero.
+  MPS_CHECK(cudaMemsetAsync(gacc, 0, n_keys * sizeof(float), st));
+  int dev = 0, sms = 148, per_sm = 0;
+  cudaGetDevice(&dev);
+  cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+  MPS_CHECK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, mps::lr_train_dense_kernel, 512, 0));
+  if (per_sm < 1) return static_cast<int>(cudaErrorLaunchOutOfResources);
+  int grid = sms * per_sm;
+  if (max_ctas > 0 && grid > max_ctas) grid = max_ctas;
+  MpsTableView v = *view;
+  MpsClockView c = *clk;
+  MpsCsr m = *csr;
+  void* args[] = {&v, &c, &worker, &start_clock, &m, &batch_starts, &n_iters, &batch, &alpha,
+                  &replica, &gacc, &loss_out};
+  MPS_CHECK(cudaLaunchCooperativeKernel(reinterpret_cast<void*>(mps::lr_train_dense_kernel), dim3(grid),
+                                        dim3(512), args, 0, st));
+  return 0;
+}

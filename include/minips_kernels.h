@@ -147,6 +147,30 @@ int mps_lr_train_dense(const MpsTableView* view, const MpsClockView* clk, int wo
                        int n_iters, int64_t batch, float alpha, float* replica, float* gacc,
                        float* loss_out, int max_ctas, void* stream);
 
+/* The same persistent training kernel as mps_lr_train_dense, for callers that cannot
+ * allocate device memory.  (No counterpart in the reference: its workers allocate freely
+ * on the host heap.)  Who needs it: an embedder whose own pool already owns all free HBM,
+ * so that a new cudaMalloc would fail; a latency-critical loop that must not take the
+ * device-wide synchronisation an allocation implies; a plain C caller with no device
+ * allocator to borrow scratch from.  The replica and the gradient accumulator live in a
+ * fixed array inside the library image instead: 2 x MPS_NOALLOC_MAX_KEYS floats (8 MiB) that
+ * every GPU loading the library holds until the process exits.
+ *   - Inputs and outputs (table views, CSR arrays, batch_starts, loss_out) are still the
+ *     caller's; nothing is allocated or freed by this call, here or in any library it uses.
+ *   - Tables with more than MPS_NOALLOC_MAX_KEYS keys are refused: the call prints the two
+ *     sizes to stderr and returns cudaErrorInvalidValue without launching anything.
+ *   - The first call on each device looks up that device's address of the array (the
+ *     device must be current).  Make that first call outside any stream capture.
+ *   - All calls on one GPU share the one array.  It keeps the previous call's contents; the
+ *     part that has to start at zero (the accumulator) is cleared on `stream` before the
+ *     launch.  Two calls that overlap on the same GPU (different streams, different tables)
+ *     race on it — serialise them. */
+#define MPS_NOALLOC_MAX_KEYS (1u << 20)
+int mps_lr_train_dense_noalloc(const MpsTableView* view, const MpsClockView* clk, int worker,
+                               int start_clock, const MpsCsr* csr, const int64_t* batch_starts,
+                               int n_iters, int64_t batch, float alpha, float* loss_out, int max_ctas,
+                               void* stream);
+
 /* Accuracy / logloss of local rows against a local full copy of the weights
  * (lr_example.cpp:61-87).  out[0] += logloss, out[1] += #correct. */
 int mps_lr_eval(const float* weights, const MpsCsr* csr, int64_t row_begin, int64_t n,
