@@ -24,7 +24,7 @@ clock_kernel(const __grid_constant__ MpsTableView v, const __grid_constant__ Mps
     fence_sys();
     for (int i = 0; i < c.num_ranks; ++i) {
       const int r = (c.my_rank + i) % c.num_ranks;
-      st_release_sys(c.pad[r] + MPS_PAD_PROGRESS + worker, new_clock);
+      st_relaxed_sys(c.pad[r] + MPS_PAD_PROGRESS + worker, new_clock);
     }
   }
   if (!fold || c.model != MPS_MODEL_BSP || c.own_count <= 0) return;
@@ -80,7 +80,7 @@ clock_kernel(const __grid_constant__ MpsTableView v, const __grid_constant__ Mps
       for (int i = 0; i < c.num_ranks; ++i) {
         const int r = (c.my_rank + i) % c.num_ranks;
         for (int s = c.own_first; s < c.own_first + c.own_count; ++s)
-          st_release_sys(c.pad[r] + MPS_PAD_FOLDED + s, new_clock);
+          st_relaxed_sys(c.pad[r] + MPS_PAD_FOLDED + s, new_clock);
       }
     }
   }
@@ -91,7 +91,7 @@ __global__ void barrier_kernel(const __grid_constant__ MpsClockView c, int epoch
   fence_sys();
   for (int i = 0; i < c.num_ranks; ++i) {
     const int r = (c.my_rank + i) % c.num_ranks;
-    st_release_sys(c.pad[r] + MPS_PAD_BARRIER + c.my_rank, epoch);
+    st_relaxed_sys(c.pad[r] + MPS_PAD_BARRIER + c.my_rank, epoch);
   }
   const int* bar = c.pad[c.my_rank] + MPS_PAD_BARRIER;
   spin_until(c, [&] {
@@ -103,7 +103,10 @@ __global__ void barrier_kernel(const __grid_constant__ MpsClockView c, int epoch
 
 __global__ void reset_pad_kernel(const __grid_constant__ MpsClockView c, int start_clock) {
   int* pad = c.pad[c.my_rank];
-  for (int i = threadIdx.x; i < MPS_MAX_WORKERS; i += blockDim.x) pad[MPS_PAD_PROGRESS + i] = start_clock;
+  for (int i = threadIdx.x; i < MPS_MAX_WORKERS; i += blockDim.x) {
+    pad[MPS_PAD_PROGRESS + i] = start_clock;
+    pad[MPS_PAD_PULLED + i] = start_clock;
+  }
   for (int i = threadIdx.x; i < MPS_MAX_SHARDS; i += blockDim.x) pad[MPS_PAD_FOLDED + i] = start_clock;
   if (threadIdx.x == 0) {
     pad[MPS_PAD_ERROR] = 0;

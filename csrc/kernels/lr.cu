@@ -68,7 +68,6 @@ lr_step_sparse_kernel(const __grid_constant__ MpsTableView v, const __grid_const
     if (ridx >= csr.n_rows) ridx %= csr.n_rows;
     const int64_t beg = csr.row_ptr[ridx], end = csr.row_ptr[ridx + 1];
     // pull + forward: two nnz per lane in flight (rows of <= 64 nnz stay in registers)
-    uint32_t c0 = 0, c1 = 0;
     float x0 = 0.f, x1 = 0.f;
     float* d0 = nullptr;
     float* d1 = nullptr;
@@ -98,9 +97,8 @@ lr_step_sparse_kernel(const __grid_constant__ MpsTableView v, const __grid_const
       }
       acc = fmaf(w0, kx0, acc);
       acc = fmaf(w1, kx1, acc);
-      if (base == beg) { c0 = kc0; c1 = kc1; x0 = kx0; x1 = kx1; d0 = p0; d1 = p1; }
+      if (base == beg) { x0 = kx0; x1 = kx1; d0 = p0; d1 = p1; }
     }
-    (void)c0; (void)c1;
     const float z = warp_sum(acc);
     const float y = csr.label[ridx];
     const float pred = sigmoidf_fast(z);
@@ -160,7 +158,9 @@ __device__ __forceinline__ void slab_pull(const MpsTableView& v, int rot_shard, 
   }
 }
 
-// slab-push gacc into the owners (vector reds), clearing gacc behind itself
+// slab-push gacc into the owners' WEIGHTS (vector reds), clearing gacc behind itself.  The
+// fused kernel adds in place even under BSP: isolation comes from the "pulled" flags (every
+// worker finished its Get of this clock before anyone adds), so no staging pass is needed.
 __device__ __forceinline__ void slab_push(const MpsTableView& v, int rot_shard, float* __restrict__ gacc,
                                           int64_t tid, int64_t nthreads) {
   const int S = v.num_shards;
@@ -169,7 +169,7 @@ __device__ __forceinline__ void slab_push(const MpsTableView& v, int rot_shard, 
     if (s >= S) s -= S;
     const int64_t fb = flat_begin1(v, s);
     const int64_t len = static_cast<int64_t>(v.begin[s + 1] - v.begin[s]);
-    float* dst = static_cast<float*>(v.staging[s] ? v.staging[s] : v.weights[s]);
+    float* dst = static_cast<float*>(v.weights[s]);
     float* src = gacc + fb;
     if ((fb & 3) == 0) {
       const int64_t len4 = len >> 2;
@@ -193,146 +193,229 @@ __device__ __forceinline__ void slab_push(const MpsTableView& v, int rot_shard, 
   }
 }
 
-// One row of the batch against a local dense copy of the weights.  kTrain: also scatter the
-// gradient into gacc (device-scope red into the local L2).
-template <bool kTrain>
-__device__ __forceinline__ void row_pass(const MpsCsr& csr, int64_t ridx, int lane,
-                                         const float* __restrict__ wloc, float* __restrict__ gacc,
-                                         float alpha, float& loss, float& correct) {
-  const int64_t beg = csr.row_ptr[ridx], end = csr.row_ptr[ridx + 1];
-  uint32_t c0 = 0, c1 = 0;
-  float x0 = 0.f, x1 = 0.f, acc = 0.f;
-  for (int64_t base = beg; base < end; base += 64) {
-    const int64_t j0 = base + lane, j1 = j0 + 32;
-    uint32_t kc0 = 0, kc1 = 0;
-    float kx0 = 0.f, kx1 = 0.f;
-    if (j0 < end) { kc0 = ld_stream(csr.col + j0); kx0 = ld_stream(csr.val + j0); }
-    if (j1 < end) { kc1 = ld_stream(csr.col + j1); kx1 = ld_stream(csr.val + j1); }
-    const float w0 = (j0 < end) ? ld_cg(wloc + kc0) : 0.f;
-    const float w1 = (j1 < end) ? ld_cg(wloc + kc1) : 0.f;
-    acc = fmaf(w0, kx0, acc);
-    acc = fmaf(w1, kx1, acc);
-    if (base == beg) { c0 = kc0; c1 = kc1; x0 = kx0; x1 = kx1; }
-  }
-  const float z = warp_sum(acc);
-  const float y = csr.label[ridx];
-  const float pred = sigmoidf_fast(z);
-  if (lane == 0) {
-    loss += logloss(z, y);
-    correct += ((pred > 0.5f) == (y > 0.5f)) ? 1.f : 0.f;
-  }
-  if (kTrain) {
-    const float g = alpha * (y - pred);
-    if (beg + lane < end && x0 != 0.f) red_gpu(gacc + c0, g * x0);
-    if (beg + lane + 32 < end && x1 != 0.f) red_gpu(gacc + c1, g * x1);
-    for (int64_t base = beg + 64; base < end; base += 64) {
-      const int64_t j0 = base + lane, j1 = j0 + 32;
-      if (j0 < end) {
-        const float kx = ld_stream(csr.val + j0);
-        if (kx != 0.f) red_gpu(gacc + ld_stream(csr.col + j0), g * kx);
-      }
-      if (j1 < end) {
-        const float kx = ld_stream(csr.val + j1);
-        if (kx != 0.f) red_gpu(gacc + ld_stream(csr.col + j1), g * kx);
+// Rows of a batch against a local dense copy of the weights.  L lanes cooperate on one row
+// (32/L rows in flight per warp), each lane keeps up to E of the row's non-zeros in
+// registers so the weight gathers of a row are all issued before the first one is used.
+// kTrain: also scatter alpha*x*(y-pred) into gacc (device-scope red into the local L2).
+constexpr int kRowRegs = 8;
+
+template <int L>
+__device__ __forceinline__ float group_sum(float v, unsigned mask) {
+#pragma unroll
+  for (int o = L / 2; o > 0; o >>= 1) v += __shfl_xor_sync(mask, v, o);
+  return v;
+}
+
+template <int L, bool kTrain>
+__device__ __forceinline__ void rows_pass(const MpsCsr& csr, int64_t row0, int64_t batch,
+                                          const float* __restrict__ wloc, float* __restrict__ gacc,
+                                          float alpha, int64_t group, int64_t ngroups, float& loss,
+                                          float& correct) {
+  constexpr int E = kRowRegs;
+  const int lane = threadIdx.x & 31;
+  const int gl = lane & (L - 1);
+  const unsigned mask = (L == 32) ? 0xffffffffu : (((1u << L) - 1u) << (lane & ~(L - 1)));
+  for (int64_t r = group; r < batch; r += ngroups) {
+    int64_t ridx = row0 + r;
+    if (ridx >= csr.n_rows) ridx %= csr.n_rows;
+    const int64_t beg = csr.row_ptr[ridx], end = csr.row_ptr[ridx + 1];
+    uint32_t c[E];
+    float x[E];
+#pragma unroll
+    for (int e = 0; e < E; ++e) {
+      const int64_t j = beg + gl + e * L;
+      c[e] = 0;
+      x[e] = 0.f;
+      if (j < end) { c[e] = ld_stream(csr.col + j); x[e] = ld_stream(csr.val + j); }
+    }
+    float w[E];
+#pragma unroll
+    for (int e = 0; e < E; ++e) w[e] = (beg + gl + e * L < end) ? ld_cg(wloc + c[e]) : 0.f;
+    float acc = 0.f;
+#pragma unroll
+    for (int e = 0; e < E; ++e) acc = fmaf(w[e], x[e], acc);
+    for (int64_t j = beg + gl + E * L; j < end; j += L)  // rows longer than L*E non-zeros
+      acc = fmaf(ld_cg(wloc + ld_stream(csr.col + j)), ld_stream(csr.val + j), acc);
+    const float z = group_sum<L>(acc, mask);
+    const float y = csr.label[ridx];
+    const float pred = sigmoidf_fast(z);
+    if (gl == 0) {
+      loss += logloss(z, y);
+      correct += ((pred > 0.5f) == (y > 0.5f)) ? 1.f : 0.f;
+    }
+    if (kTrain) {
+      const float g = alpha * (y - pred);
+#pragma unroll
+      for (int e = 0; e < E; ++e)
+        if (x[e] != 0.f) red_gpu(gacc + c[e], g * x[e]);
+      for (int64_t j = beg + gl + E * L; j < end; j += L) {
+        const float kx = ld_stream(csr.val + j);
+        if (kx != 0.f) red_gpu(gacc + ld_stream(csr.col + j), g * kx);
       }
     }
   }
 }
 
+__device__ __forceinline__ unsigned long long globaltimer_ns() {
+  unsigned long long t;
+  asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t));
+  return t;
+}
+
+// min over the local replica of the "pulled" table
+__device__ __forceinline__ int pad_min_pulled(const MpsClockView& c) {
+  const int* p = c.pad[c.my_rank] + MPS_PAD_PULLED;
+  int m = 0x7fffffff;
+  for (int w = 0; w < c.num_workers; ++w) {
+    const int q = ld_acquire_sys(p + w);
+    m = q < m ? q : m;
+  }
+  return m;
+}
+
+// Persistent training kernel.  Per iteration (clock p):
+//   A  gate:  BSP min(progress) >= p | SSP p <= min + s | ASP none      (local spins)
+//   B  Get :  slab-pull all shards -> replica                        --- grid sync 1
+//      publish pulled[worker] = p+1 on every rank (BSP only)
+//   C  rows:  SpMV + sigmoid + gradient into gacc                    --- grid sync 2
+//   D  Add :  BSP waits min(pulled) >= p+1 (every worker holds its snapshot, so in-place
+//             adds cannot leak into a Get of clock p — the isolation BSPModel gets from
+//             buffering adds, bsp_model.cpp:34-43), then slab-push in place
+//   E  Clock: the LAST CTA to finish its part of the push publishes progress[worker] = p+1
+//             (release.sys) on every rank; nobody waits for it here — the next gate does.
+// timeline (optional, 8 slots per iteration): globaltimer at the phase boundaries, CTA 0.
+template <int L>
 __global__ void __launch_bounds__(512, 2)
 lr_train_dense_kernel(const __grid_constant__ MpsTableView v, const __grid_constant__ MpsClockView c,
                       int worker, int start_clock, const __grid_constant__ MpsCsr csr,
                       const int64_t* __restrict__ batch_starts, int n_iters, int64_t batch, float alpha,
-                      float* __restrict__ replica, float* __restrict__ gacc, float* __restrict__ loss_out) {
-  cg::grid_group grid = cg::this_grid();
+                      float* __restrict__ replica, float* __restrict__ gacc, float* __restrict__ loss_out,
+                      unsigned long long* __restrict__ timeline) {
   const int64_t tid = static_cast<int64_t>(blockIdx.x) * blockDim.x + threadIdx.x;
   const int64_t nthreads = static_cast<int64_t>(gridDim.x) * blockDim.x;
-  const int lane = threadIdx.x & 31;
-  const int64_t warp = tid >> 5, nwarps = nthreads >> 5;
-  const bool bsp_owner = (c.model == MPS_MODEL_BSP) && c.own_count > 0;
+  const bool bsp = (c.model == MPS_MODEL_BSP);
+  const bool multi = c.num_ranks > 1;
+  int* pad = c.pad[c.my_rank];
+  GridBarrier grid{pad + MPS_PAD_LOCALCTR + 2, 0};  // zeroed by the host before the launch
+  const bool tl = timeline != nullptr && tid == 0;
 
   for (int it = 0; it < n_iters; ++it) {
     const int p = start_clock + it;
-    // A. consistency gate for the Get of clock p (spins on the local pad only)
-    cta_gate(c, p);
-    // B. pull: every shard -> replica (KVClientTable::Get of all keys, fused)
+    if (tl) timeline[8 * it + 0] = globaltimer_ns();
+    // A. gate
+    if (threadIdx.x == 0) {
+      if (bsp) spin_until(c, [&] { return pad_min_clock(c) >= p; });
+      else spin_until(c, [&] { return gate_open(c, p); });
+    }
+    __syncthreads();
+    if (tl) timeline[8 * it + 1] = globaltimer_ns();
+    // B. Get
     slab_pull(v, c.own_first, replica, tid, nthreads);
     grid.sync();
-    // C. forward SpMV + sigmoid + gradient, accumulated locally
-    float loss = 0.f, correct = 0.f;
-    const int64_t row0 = batch_starts[it];
-    for (int64_t r = warp; r < batch; r += nwarps) {
-      int64_t ridx = row0 + r;
-      if (ridx >= csr.n_rows) ridx %= csr.n_rows;
-      row_pass<true>(csr, ridx, lane, replica, gacc, alpha, loss, correct);
-    }
-    block_accumulate(loss, correct, loss_out + 2 * it);
-    grid.sync();
-    // D. push: gacc -> owners (KVClientTable::Add of all touched keys, fused)
-    slab_push(v, c.own_first, gacc, tid, nthreads);
-    __threadfence_system();
-    grid.sync();
-    // E. Clock: publish progress[worker] = p + 1 on every replica
-    if (tid == 0) {
-      fence_sys();
+    if (tl) timeline[8 * it + 2] = globaltimer_ns();
+    if (bsp && tid == 0) {
+      // nothing to publish but "my loads are done" (the barrier above retired them): relaxed
       for (int i = 0; i < c.num_ranks; ++i) {
         const int r = (c.my_rank + i) % c.num_ranks;
-        st_release_sys(c.pad[r] + MPS_PAD_PROGRESS + worker, p + 1);
+        st_relaxed_sys(c.pad[r] + MPS_PAD_PULLED + worker, p + 1);
       }
     }
-    // F. BSP clock edge at the owner: wait for all workers, fold, publish
-    if (bsp_owner) {
-      __shared__ int ok;
-      if (threadIdx.x == 0) ok = spin_until(c, [&] { return pad_min_clock(c) >= p + 1; }) ? 1 : 0;
+    // C. rows
+    float loss = 0.f, correct = 0.f;
+    rows_pass<L, true>(csr, batch_starts[it], batch, replica, gacc, alpha, tid / L, nthreads / L, loss,
+                       correct);
+    block_accumulate(loss, correct, loss_out + 2 * it);
+    grid.sync();
+    if (tl) timeline[8 * it + 3] = globaltimer_ns();
+    // D. Add
+    if (bsp) {
+      if (threadIdx.x == 0) spin_until(c, [&] { return pad_min_pulled(c) >= p + 1; });
       __syncthreads();
-      if (ok) {
-        for (int s = c.own_first; s < c.own_first + c.own_count; ++s) {
-          if (!v.staging[s]) continue;
-          const int64_t len = static_cast<int64_t>(v.begin[s + 1] - v.begin[s]);
-          float* w = static_cast<float*>(v.weights[s]);
-          float* st = static_cast<float*>(v.staging[s]);
-          const int64_t len4 = len >> 2;
-          for (int64_t i = tid; i < len4; i += nthreads) {
-            const float4 d = ld_cg_v4(st + 4 * i);
-            if (d.x != 0.f || d.y != 0.f || d.z != 0.f || d.w != 0.f) {
-              float4 x = *reinterpret_cast<float4*>(w + 4 * i);
-              x.x += d.x; x.y += d.y; x.z += d.z; x.w += d.w;
-              *reinterpret_cast<float4*>(w + 4 * i) = x;
-              *reinterpret_cast<float4*>(st + 4 * i) = make_float4(0.f, 0.f, 0.f, 0.f);
-            }
-          }
-          for (int64_t i = (len4 << 2) + tid; i < len; i += nthreads) {
-            const float d = ld_cg(st + i);
-            if (d != 0.f) { w[i] += d; st[i] = 0.f; }
-          }
-        }
-      }
-      grid.sync();
-      if (tid == 0 && ok) {
-        fence_sys();
+    }
+    if (tl) timeline[8 * it + 4] = globaltimer_ns();
+    slab_push(v, c.own_first, gacc, tid, nthreads);
+    if (tl) timeline[8 * it + 6] = globaltimer_ns();
+    // E. Clock — last CTA out signals.  bar.sync orders the CTA's reds before thread 0's
+    //    system fence (fence cumulativity), the atomic counter orders CTAs.
+    __syncthreads();
+    if (threadIdx.x == 0) {
+      // MEMBAR.SYS costs ~4 us on B200; with a single rank every observer is on this GPU
+      // and a device-scope fence orders the reds just as well.
+      if (multi) fence_sys(); else __threadfence();
+      const int done = atomicAdd(pad + MPS_PAD_LOCALCTR + 1, 1) + 1;
+      if (done == static_cast<int>(gridDim.x)) {
+        pad[MPS_PAD_LOCALCTR + 1] = 0;
+        // Every CTA's reds were performed system-wide (its own fence above) before its arrival
+        // became visible, so a device-scope fence is enough to order the flag stores after
+        // all of them; relaxed stores avoid a MEMBAR.SYS per store.
+        __threadfence();
         for (int i = 0; i < c.num_ranks; ++i) {
           const int r = (c.my_rank + i) % c.num_ranks;
-          for (int s = c.own_first; s < c.own_first + c.own_count; ++s)
-            st_release_sys(c.pad[r] + MPS_PAD_FOLDED + s, p + 1);
+          st_relaxed_sys(c.pad[r] + MPS_PAD_PROGRESS + worker, p + 1);
         }
+      }
+    }
+    if (tl) timeline[8 * it + 5] = globaltimer_ns();
+  }
+
+  // Keep the generic Get gate (folded[s] >= clock) usable after a fused run: once every
+  // worker reached the final clock the owner republishes folded for its shards (nothing
+  // is left in staging — the fused kernel never writes there).
+  if (bsp && c.own_count > 0 && tid == 0) {
+    const int fin = start_clock + n_iters;
+    if (spin_until(c, [&] { return pad_min_clock(c) >= fin; })) {
+      if (multi) fence_sys(); else __threadfence();
+      for (int i = 0; i < c.num_ranks; ++i) {
+        const int r = (c.my_rank + i) % c.num_ranks;
+        for (int s = c.own_first; s < c.own_first + c.own_count; ++s)
+          st_relaxed_sys(c.pad[r] + MPS_PAD_FOLDED + s, fin);
       }
     }
   }
 }
 
+template <int L>
 __global__ void __launch_bounds__(256)
 lr_eval_kernel(const float* __restrict__ weights, const __grid_constant__ MpsCsr csr, int64_t row_begin,
                int64_t n, float* __restrict__ out) {
-  const int lane = threadIdx.x & 31;
-  const int64_t warp = (static_cast<int64_t>(blockIdx.x) * blockDim.x + threadIdx.x) >> 5;
-  const int64_t nwarps = (static_cast<int64_t>(gridDim.x) * blockDim.x) >> 5;
+  const int64_t tid = static_cast<int64_t>(blockIdx.x) * blockDim.x + threadIdx.x;
+  const int64_t nthreads = static_cast<int64_t>(gridDim.x) * blockDim.x;
   float loss = 0.f, correct = 0.f;
-  for (int64_t r = warp; r < n; r += nwarps) {
-    int64_t ridx = row_begin + r;
-    if (ridx >= csr.n_rows) ridx %= csr.n_rows;
-    row_pass<false>(csr, ridx, lane, weights, nullptr, 0.f, loss, correct);
-  }
+  rows_pass<L, false>(csr, row_begin, n, weights, nullptr, 0.f, tid / L, nthreads / L, loss, correct);
   block_accumulate(loss, correct, out);
+}
+
+// lanes per row from the average row length: 8 lanes hold rows of <= 64 nnz in registers
+static int lanes_for(int64_t avg_nnz) {
+  if (avg_nnz <= 8 * kRowRegs) return 8;
+  if (avg_nnz <= 16 * kRowRegs) return 16;
+  return 32;
+}
+
+static int launch_dense(const MpsTableView* view, const MpsClockView* clk, int worker, int start_clock,
+                        const MpsCsr* csr, const int64_t* batch_starts, int n_iters, int64_t batch,
+                        float alpha, float* replica, float* gacc, float* loss_out,
+                        unsigned long long* timeline, int avg_nnz, int max_ctas, cudaStream_t st) {
+  int dev = 0, sms = 148, per_sm = 0;
+  cudaGetDevice(&dev);
+  cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+  const int L = lanes_for(avg_nnz > 0 ? avg_nnz : 40);
+  void* fn = L == 8 ? reinterpret_cast<void*>(lr_train_dense_kernel<8>)
+                    : (L == 16 ? reinterpret_cast<void*>(lr_train_dense_kernel<16>)
+                               : reinterpret_cast<void*>(lr_train_dense_kernel<32>));
+  MPS_CHECK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, fn, 512, 0));
+  if (per_sm < 1) return static_cast<int>(cudaErrorLaunchOutOfResources);
+  int grid = sms * per_sm;
+  if (max_ctas > 0 && grid > max_ctas) grid = max_ctas;
+  MpsTableView v = *view;
+  MpsClockView c = *clk;
+  MpsCsr m = *csr;
+  void* args[] = {&v, &c, &worker, &start_clock, &m, &batch_starts, &n_iters, &batch, &alpha,
+                  &replica, &gacc, &loss_out, &timeline};
+  // arrival counter of the in-kernel grid barrier starts at zero
+  MPS_CHECK(cudaMemsetAsync(c.pad[c.my_rank] + MPS_PAD_LOCALCTR + 2, 0, sizeof(int), st));
+  MPS_CHECK(cudaLaunchCooperativeKernel(fn, dim3(grid), dim3(512), args, 0, st));
+  return 0;
 }
 
 }  // namespace mps
@@ -363,21 +446,18 @@ int mps_lr_train_dense(const MpsTableView* view, const MpsClockView* clk, int wo
                        void* stream) {
   if (n_iters <= 0) return 0;
   if (view->dtype != MPS_F32 || view->vals_per_key != 1) return static_cast<int>(cudaErrorInvalidValue);
-  int dev = 0, sms = 148, per_sm = 0;
-  cudaGetDevice(&dev);
-  cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
-  MPS_CHECK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, mps::lr_train_dense_kernel, 512, 0));
-  if (per_sm < 1) return static_cast<int>(cudaErrorLaunchOutOfResources);
-  int grid = sms * per_sm;
-  if (max_ctas > 0 && grid > max_ctas) grid = max_ctas;
-  MpsTableView v = *view;
-  MpsClockView c = *clk;
-  MpsCsr m = *csr;
-  void* args[] = {&v, &c, &worker, &start_clock, &m, &batch_starts, &n_iters, &batch, &alpha,
-                  &replica, &gacc, &loss_out};
-  MPS_CHECK(cudaLaunchCooperativeKernel(reinterpret_cast<void*>(mps::lr_train_dense_kernel), dim3(grid),
-                                        dim3(512), args, 0, static_cast<cudaStream_t>(stream)));
-  return 0;
+  return mps::launch_dense(view, clk, worker, start_clock, csr, batch_starts, n_iters, batch, alpha, replica,
+                           gacc, loss_out, nullptr, 0, max_ctas, static_cast<cudaStream_t>(stream));
+}
+
+int mps_lr_train_dense_ex(const MpsTableView* view, const MpsClockView* clk, int worker, int start_clock,
+                          const MpsCsr* csr, const int64_t* batch_starts, int n_iters, int64_t batch,
+                          float alpha, float* replica, float* gacc, float* loss_out,
+                          unsigned long long* timeline, int avg_nnz, int max_ctas, void* stream) {
+  if (n_iters <= 0) return 0;
+  if (view->dtype != MPS_F32 || view->vals_per_key != 1) return static_cast<int>(cudaErrorInvalidValue);
+  return mps::launch_dense(view, clk, worker, start_clock, csr, batch_starts, n_iters, batch, alpha, replica,
+                           gacc, loss_out, timeline, avg_nnz, max_ctas, static_cast<cudaStream_t>(stream));
 }
 
 int mps_lr_eval(const float* weights, const MpsCsr* csr, int64_t row_begin, int64_t n, float* out,
@@ -386,9 +466,9 @@ int mps_lr_eval(const float* weights, const MpsCsr* csr, int64_t row_begin, int6
   int dev = 0, sms = 148;
   cudaGetDevice(&dev);
   cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
-  int64_t want = (n + 7) / 8;
+  int64_t want = (n + 31) / 32;  // 32 row groups of 8 lanes per 256-thread CTA
   const int grid = static_cast<int>(want < sms * 8 ? want : sms * 8);
-  mps::lr_eval_kernel<<<grid, 256, 0, static_cast<cudaStream_t>(stream)>>>(weights, *csr, row_begin, n, out);
+  mps::lr_eval_kernel<8><<<grid, 256, 0, static_cast<cudaStream_t>(stream)>>>(weights, *csr, row_begin, n, out);
   MPS_LAUNCH_CHECK();
   return 0;
 }
@@ -455,19 +535,6 @@ extern "C" int mps_lr_train_dense_noalloc(const MpsTableView* view, const MpsClo
   // The array still holds whatever the previous call left.  The replica is overwritten by the
   // slab pull before it is read; the gradient accumulator must start at zero.
   MPS_CHECK(cudaMemsetAsync(gacc, 0, n_keys * sizeof(float), st));
-  int dev = 0, sms = 148, per_sm = 0;
-  cudaGetDevice(&dev);
-  cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
-  MPS_CHECK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, mps::lr_train_dense_kernel, 512, 0));
-  if (per_sm < 1) return static_cast<int>(cudaErrorLaunchOutOfResources);
-  int grid = sms * per_sm;
-  if (max_ctas > 0 && grid > max_ctas) grid = max_ctas;
-  MpsTableView v = *view;
-  MpsClockView c = *clk;
-  MpsCsr m = *csr;
-  void* args[] = {&v, &c, &worker, &start_clock, &m, &batch_starts, &n_iters, &batch, &alpha,
-                  &replica, &gacc, &loss_out};
-  MPS_CHECK(cudaLaunchCooperativeKernel(reinterpret_cast<void*>(mps::lr_train_dense_kernel), dim3(grid),
-                                        dim3(512), args, 0, st));
-  return 0;
+  return mps::launch_dense(view, clk, worker, start_clock, csr, batch_starts, n_iters, batch, alpha, replica,
+                           gacc, loss_out, nullptr, 0, max_ctas, st);
 }

@@ -25,12 +25,13 @@ extern "C" {
 
 /* Signal-pad layout (int32 slots) inside each rank's symmetric pad, one pad per table. */
 #define MPS_PAD_PROGRESS 0                                   /* [MPS_MAX_WORKERS] worker clocks   */
-#define MPS_PAD_FOLDED (MPS_PAD_PROGRESS + MPS_MAX_WORKERS)  /* [MPS_MAX_SHARDS]  BSP fold clocks */
+#define MPS_PAD_PULLED (MPS_PAD_PROGRESS + MPS_MAX_WORKERS)  /* [MPS_MAX_WORKERS] "Get of clock p done" = p+1 */
+#define MPS_PAD_FOLDED (MPS_PAD_PULLED + MPS_MAX_WORKERS)    /* [MPS_MAX_SHARDS]  BSP fold clocks */
 #define MPS_PAD_BARRIER (MPS_PAD_FOLDED + MPS_MAX_SHARDS)    /* [MPS_MAX_RANKS]   barrier epochs  */
 #define MPS_PAD_ERROR (MPS_PAD_BARRIER + MPS_MAX_RANKS)      /* [1] sticky error (timeout) flag   */
 #define MPS_PAD_MINCLOCK (MPS_PAD_ERROR + 1)                 /* [1] last min clock seen (debug)   */
 #define MPS_PAD_LOCALCTR (MPS_PAD_MINCLOCK + 1)              /* [4] local CTA-completion counters */
-#define MPS_PAD_INTS 512                                     /* pad size in int32 (2 KiB)         */
+#define MPS_PAD_INTS 1024                                    /* pad size in int32 (4 KiB)         */
 
 enum { MPS_MODEL_SSP = 0, MPS_MODEL_BSP = 1, MPS_MODEL_ASP = 2 }; /* driver/engine.hpp:25-27 */
 enum { MPS_F32 = 0, MPS_F64 = 1 };
@@ -146,6 +147,16 @@ int mps_lr_train_dense(const MpsTableView* view, const MpsClockView* clk, int wo
                        int start_clock, const MpsCsr* csr, const int64_t* batch_starts,
                        int n_iters, int64_t batch, float alpha, float* replica, float* gacc,
                        float* loss_out, int max_ctas, void* stream);
+
+/* mps_lr_train_dense plus observability / tuning knobs: `timeline` (NULL or 8 uint64 per
+ * iteration) receives %globaltimer at the phase boundaries gate|pull|sync1|rows+sync2|
+ * pulled-wait|push (the per-phase timers SURVEY 5.1 asks for); avg_nnz picks the lanes per
+ * row (8/16/32; 0 = 40 nnz default). */
+int mps_lr_train_dense_ex(const MpsTableView* view, const MpsClockView* clk, int worker,
+                          int start_clock, const MpsCsr* csr, const int64_t* batch_starts,
+                          int n_iters, int64_t batch, float alpha, float* replica, float* gacc,
+                          float* loss_out, unsigned long long* timeline, int avg_nnz, int max_ctas,
+                          void* stream);
 
 /* The same persistent training kernel as mps_lr_train_dense, for callers that cannot
  * allocate device memory.  (No counterpart in the reference: its workers allocate freely

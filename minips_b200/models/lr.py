@@ -95,6 +95,7 @@ class SparseLRTrainer:
         self.dev = client.dev
         self._replica: Optional[torch.Tensor] = None
         self._gacc: Optional[torch.Tensor] = None
+        self.avg_nnz = max(1, int(round(data.nnz / max(1, data.n_rows))))
         assert self.table.dtype == torch.float32 and self.table.k == 1
 
     def _scratch(self):
@@ -110,7 +111,8 @@ class SparseLRTrainer:
         return batch * nnz_per_row * 4 >= self.table.num_keys
 
     def train_dense(self, batch_starts: torch.Tensor, batch: int, max_ctas: int = 0,
-                    csr: Optional[_lib.Csr] = None, loss: Optional[torch.Tensor] = None) -> torch.Tensor:
+                    csr: Optional[_lib.Csr] = None, loss: Optional[torch.Tensor] = None,
+                    timeline: Optional[torch.Tensor] = None) -> torch.Tensor:
         """Run len(batch_starts) iterations inside one persistent kernel.  Returns the per-
         iteration (logloss sum, #correct) tensor [n_iters, 2] (device, async)."""
         c = self.client
@@ -123,11 +125,12 @@ class SparseLRTrainer:
         if csr is None:
             csr = self.data.c_struct()
         c._local_gate()
-        _lib.check(self.lib.mps_lr_train_dense(
+        tl_ptr = C.c_void_p(timeline.data_ptr()) if timeline is not None else None
+        _lib.check(self.lib.mps_lr_train_dense_ex(
             C.byref(t.view), C.byref(cv), c.worker_id, c.progress, C.byref(csr),
             C.c_void_p(batch_starts.data_ptr()), n_iters, batch, self.alpha,
             C.c_void_p(replica.data_ptr()), C.c_void_p(gacc.data_ptr()), C.c_void_p(loss.data_ptr()),
-            max_ctas, c._sp()), "lr_train_dense")
+            tl_ptr, self.avg_nnz, max_ctas, c._sp()), "lr_train_dense")
         # host mirror of the clock (the kernel published the device-side one)
         with t.lock:
             c.progress += n_iters

@@ -14,12 +14,13 @@ MAX_SHARDS = 64
 MAX_RANKS = 16
 MAX_WORKERS = 256
 PAD_PROGRESS = 0
-PAD_FOLDED = PAD_PROGRESS + MAX_WORKERS
+PAD_PULLED = PAD_PROGRESS + MAX_WORKERS
+PAD_FOLDED = PAD_PULLED + MAX_WORKERS
 PAD_BARRIER = PAD_FOLDED + MAX_SHARDS
 PAD_ERROR = PAD_BARRIER + MAX_RANKS
 PAD_MINCLOCK = PAD_ERROR + 1
 PAD_LOCALCTR = PAD_MINCLOCK + 1
-PAD_INTS = 512
+PAD_INTS = 1024
 
 MODEL_SSP, MODEL_BSP, MODEL_ASP = 0, 1, 2
 F32, F64 = 0, 1
@@ -119,6 +120,8 @@ def _declare(lib):
         "mps_lr_step_sparse": ([P(TableView), P(ClockView), i32, i32, P(Csr), i64, i64, f32, vp, vp], i32),
         "mps_lr_train_dense": ([P(TableView), P(ClockView), i32, i32, P(Csr), vp, i32, i64, f32, vp, vp, vp,
                                 i32, vp], i32),
+        "mps_lr_train_dense_ex": ([P(TableView), P(ClockView), i32, i32, P(Csr), vp, i32, i64, f32, vp, vp, vp,
+                                   vp, i32, i32, vp], i32),
         "mps_lr_eval": ([vp, P(Csr), i64, i64, vp, vp], i32),
     }
     for name, (argtypes, restype) in sig.items():
