@@ -132,9 +132,12 @@ def build_core(force=False, verbose=True):
     # executables
     bin_dir = BUILD / "bin"
     bin_dir.mkdir(parents=True, exist_ok=True)
-    app_dir = ROOT / "csrc" / "apps"
-    if app_dir.exists():
-        for s in sorted(app_dir.glob("*.cpp")):
+    exe_srcs = []
+    for d in (ROOT / "csrc" / "apps", ROOT / "csrc" / "tests"):
+        if d.exists():
+            exe_srcs.extend(sorted(d.glob("*.cpp")))
+    if exe_srcs:
+        for s in exe_srcs:
             exe = bin_dir / s.stem
             if force or jobs or _newer([s, *hdrs], exe):
                 _run([CXX, *CXX_FLAGS, s, *objs, "-o", exe, "-pthread"])

@@ -1,0 +1,1381 @@
+// core_tests.cpp — unit / integration tests of the C++ host runtime.
+//
+// Part 1 restates, case by case, the behaviour pinned by the reference's 50 gtest cases
+// (file:line cited per case); part 2 covers what the reference leaves untested (SURVEY §4:
+// VectorStorage dump format, Context, node_utils, BinStream, SArray, queue, WorkerThread,
+// master, io, lib).  No gtest in this image: a 40-line harness below.  Run one case with
+// `core_tests <filter-substring>`; pytest drives it through tests/test_core_cpp.py.
+#include <unistd.h>
+
+#include <cmath>
+#include <cstdio>
+#include <fstream>
+#include <functional>
+#include <iostream>
+#include <string>
+#include <vector>
+
+#include "core/bin_stream.hpp"
+#include "core/checkpoint_io.hpp"
+#include "core/driver.hpp"
+#include "core/file_io.hpp"
+#include "core/io.hpp"
+#include "core/lib.hpp"
+#include "core/master.hpp"
+#include "core/node_utils.hpp"
+
+using namespace minips;  // NOLINT
+
+// ------------------------------------------------------------------ harness
+struct TestCase {
+  std::string name;
+  std::function<void()> fn;
+};
+static std::vector<TestCase>& Registry() {
+  static std::vector<TestCase> r;
+  return r;
+}
+struct Registrar {
+  Registrar(const std::string& name, std::function<void()> fn) { Registry().push_back({name, std::move(fn)}); }
+};
+static int g_failures = 0;
+#define TEST(suite, name)                                           \
+  static void suite##_##name();                                     \
+  static Registrar reg_##suite##_##name(#suite "." #name, suite##_##name); \
+  static void suite##_##name()
+#define EXPECT_TRUE(c)                                                                     \
+  do {                                                                                     \
+    if (!(c)) {                                                                            \
+      ++g_failures;                                                                        \
+      std::cerr << "    " << __FILE__ << ":" << __LINE__ << " EXPECT_TRUE(" #c ") failed\n"; \
+    }                                                                                      \
+  } while (0)
+#define EXPECT_EQ(a, b)                                                                             \
+  do {                                                                                              \
+    auto _a = (a);                                                                                  \
+    auto _b = (b);                                                                                  \
+    if (!(_a == _b)) {                                                                              \
+      ++g_failures;                                                                                 \
+      std::cerr << "    " << __FILE__ << ":" << __LINE__ << " EXPECT_EQ(" #a ", " #b "): " << _a << " vs " << _b \
+                << "\n";                                                                            \
+    }                                                                                               \
+  } while (0)
+#define EXPECT_NEAR(a, b, tol) EXPECT_TRUE(std::fabs((a) - (b)) <= (tol))
+#define EXPECT_THROW(stmt)                   \
+  do {                                       \
+    bool _t = false;                         \
+    try {                                    \
+      stmt;                                  \
+    } catch (const std::exception&) {        \
+      _t = true;                             \
+    }                                        \
+    EXPECT_TRUE(_t);                         \
+  } while (0)
+
+static Message Msg(Flag f, int sender, int recver, int model = 0) {
+  Message m;
+  m.meta.flag = f;
+  m.meta.sender = sender;
+  m.meta.recver = recver;
+  m.meta.model_id = model;
+  return m;
+}
+template <typename V>
+static Message GetMsg(int sender, std::initializer_list<V> keys) {
+  Message m = Msg(Flag::kGet, sender, 0);
+  m.AddData(SArray<V>(keys));
+  return m;
+}
+template <typename V>
+static Message AddMsg(int sender, std::initializer_list<V> keys, std::initializer_list<V> vals) {
+  Message m = Msg(Flag::kAdd, sender, 0);
+  m.AddData(SArray<V>(keys));
+  m.AddData(SArray<V>(vals));
+  return m;
+}
+static void ResetWorkers(AbstractModel* model, ThreadsafeQueue<Message>* q, std::initializer_list<uint32_t> tids) {
+  Message reset;
+  reset.AddData(SArray<uint32_t>(tids));
+  model->ResetWorker(reset);
+  Message ack;
+  EXPECT_EQ(q->Size(), 1);
+  q->WaitAndPop(&ack);
+  EXPECT_TRUE(ack.meta.flag == Flag::kResetWorkerInModel);
+}
+static int PortBase() { return 20000 + (static_cast<int>(::getpid()) % 1000) * 20; }
+static std::string TmpDir() {
+  std::string d = "/tmp/minips_core_tests_" + std::to_string(::getpid()) + "/";
+  io::MakeDirsFor(d + "x");
+  return d;
+}
+
+// ================================================================== part 1: reference cases
+// base/message_test.cpp:22-27
+TEST(Message, BasicNotBreakDown) {
+  Message m;
+  m.AddData(SArray<int>({1, 2, 3}));
+  EXPECT_EQ(m.data.size(), 1u);
+  EXPECT_EQ(m.data[0].size(), 12u);
+  EXPECT_TRUE(!m.DebugString().empty());
+}
+
+// base/range_partition_manager_test.cpp:21-64
+TEST(RangePartitionManager, Init) { RangePartitionManager pm({0, 1, 2}, {{2, 4}, {4, 7}, {7, 10}}); EXPECT_EQ(pm.GetNumServers(), 3u); }
+TEST(RangePartitionManager, SliceKeys) {
+  RangePartitionManager pm({0, 1, 2}, {{2, 4}, {4, 7}, {7, 10}});
+  SArray<Key> keys({2, 8, 9});
+  std::vector<std::pair<int, SArray<Key>>> sliced;
+  pm.Slice(keys, &sliced);
+  EXPECT_EQ(sliced.size(), 2u);  // server 1 gets nothing and is skipped
+  EXPECT_EQ(sliced[0].first, 0);
+  EXPECT_EQ(sliced[1].first, 2);
+  EXPECT_EQ(sliced[0].second.size(), 1u);
+  EXPECT_EQ(sliced[1].second.size(), 2u);
+  EXPECT_EQ(sliced[0].second[0], 2u);
+  EXPECT_EQ(sliced[1].second[0], 8u);
+  EXPECT_EQ(sliced[1].second[1], 9u);
+}
+TEST(RangePartitionManager, SliceKVs) {
+  RangePartitionManager pm({0, 1, 2}, {{2, 4}, {4, 7}, {7, 10}});
+  SArray<Key> keys({2, 5, 9});
+  SArray<double> vals({0.2, 0.5, 0.9});
+  std::vector<std::pair<int, AbstractPartitionManager::KVPairs>> sliced;
+  pm.Slice(std::make_pair(keys, vals), &sliced);
+  EXPECT_EQ(sliced.size(), 3u);
+  for (int i = 0; i < 3; ++i) {
+    EXPECT_EQ(sliced[i].first, i);
+    EXPECT_EQ(sliced[i].second.first.size(), 1u);
+    EXPECT_EQ(sliced[i].second.first[0], keys[i]);
+    EXPECT_NEAR(sliced[i].second.second[0], vals[i], 1e-12);
+  }
+}
+
+// driver/simple_id_mapper_test.cpp:22-75
+TEST(SimpleIdMapper, Init) {
+  Node n1{0, "localhost", 12351}, n2{1, "localhost", 12352}, n3{3, "localhost", 12353};
+  SimpleIdMapper m(n1, {n1, n2, n3});
+  m.Init(2);
+  EXPECT_EQ(m.GetNodeIdForThread(0), 0u);
+  EXPECT_EQ(m.GetNodeIdForThread(1000), 1u);
+  EXPECT_EQ(m.GetNodeIdForThread(3050), 3u);
+  EXPECT_TRUE(m.GetServerThreadsForId(0) == std::vector<uint32_t>({0, 1}));
+  EXPECT_TRUE(m.GetServerThreadsForId(1) == std::vector<uint32_t>({1000, 1001}));
+  EXPECT_TRUE(m.GetServerThreadsForId(3) == std::vector<uint32_t>({3000, 3001}));
+  EXPECT_TRUE(m.GetWorkerHelperThreadsForId(0) == std::vector<uint32_t>({50}));
+  EXPECT_TRUE(m.GetWorkerHelperThreadsForId(3) == std::vector<uint32_t>({3050}));
+  EXPECT_TRUE(m.GetAllServerThreads() == std::vector<uint32_t>({0, 1, 1000, 1001, 3000, 3001}));
+}
+TEST(SimpleIdMapper, AllocateDeallocateThread) {
+  Node n1{0, "localhost", 12351}, n2{1, "localhost", 12352};
+  SimpleIdMapper m(n1, {n1, n2});
+  m.Init(1);
+  EXPECT_EQ(m.AllocateWorkerThread(0), 100u);
+  EXPECT_EQ(m.AllocateWorkerThread(0), 101u);
+  EXPECT_EQ(m.AllocateWorkerThread(1), 1100u);
+  EXPECT_EQ(m.AllocateWorkerThread(1), 1101u);
+  EXPECT_EQ(m.AllocateWorkerThread(1), 1102u);
+  EXPECT_EQ(m.GetWorkerThreadsForId(1).size(), 3u);
+  m.DeallocateWorkerThread(1, 1101);
+  EXPECT_TRUE(m.GetWorkerThreadsForId(1) == std::vector<uint32_t>({1100, 1102}));
+  EXPECT_EQ(m.AllocateWorkerThread(1), 1101u);
+}
+
+// driver/worker_spec_test.cpp:23-86
+TEST(WorkerSpec, Init) { WorkerSpec spec({{0, 10}, {1, 20}}); EXPECT_EQ(spec.GetNumWorkers(), 30u); }
+TEST(WorkerSpec, GetWorker) {
+  WorkerSpec spec({{0, 3}, {1, 2}});
+  EXPECT_TRUE(spec.HasLocalWorkers(0));
+  EXPECT_TRUE(spec.HasLocalWorkers(1));
+  EXPECT_TRUE(!spec.HasLocalWorkers(2));
+  EXPECT_TRUE(spec.GetLocalWorkers(0) == std::vector<uint32_t>({0, 1, 2}));
+  EXPECT_TRUE(spec.GetLocalWorkers(1) == std::vector<uint32_t>({3, 4}));
+  EXPECT_EQ(spec.GetWorkerToNodeMapper().at(3), 1u);
+}
+TEST(WorkerSpec, InsertWorkerIdThreadId) {
+  WorkerSpec spec({{0, 3}, {1, 2}});
+  spec.InsertWorkerIdThreadId(0, 100);
+  spec.InsertWorkerIdThreadId(1, 101);
+  spec.InsertWorkerIdThreadId(3, 1100);
+  EXPECT_TRUE(spec.GetAllThreadIds() == std::vector<uint32_t>({100, 101, 1100}));
+  EXPECT_TRUE(spec.GetLocalThreads(0) == std::vector<uint32_t>({100, 101}));
+  EXPECT_TRUE(spec.GetLocalThreads(1) == std::vector<uint32_t>({1100}));
+  EXPECT_EQ(spec.GetWorkerToThreadMapper().at(3), 1100u);
+  EXPECT_EQ(spec.GetThreadToWorkerMapper().at(101), 1u);
+  EXPECT_THROW(spec.InsertWorkerIdThreadId(0, 102));
+}
+
+// server/map_storage_test.cpp:21-77
+TEST(MapStorage, AddGetInt) {
+  MapStorage<int> s;
+  Message a = AddMsg<int>(0, {13, 14, 15}, {1, 2, 3});
+  s.Add(a);
+  s.Add(a);
+  Message g = GetMsg<int>(5, {13, 15, 99});
+  g.meta.recver = 7;
+  Message r = s.Get(g);
+  EXPECT_EQ(r.meta.sender, 7);
+  EXPECT_EQ(r.meta.recver, 5);
+  SArray<int> vals(r.data[1]);
+  EXPECT_EQ(vals.size(), 3u);
+  EXPECT_EQ(vals[0], 2);
+  EXPECT_EQ(vals[1], 6);
+  EXPECT_EQ(vals[2], 0);
+}
+TEST(MapStorage, AddGetFloat) {
+  MapStorage<float> s;
+  Message a = Msg(Flag::kAdd, 0, 0);
+  a.AddData(SArray<Key>({1, 2}));
+  a.AddData(SArray<float>({0.5f, 0.25f}));
+  s.Add(a);
+  Message g = Msg(Flag::kGet, 0, 0);
+  g.AddData(SArray<Key>({1, 2}));
+  SArray<float> vals(s.Get(g).data[1]);
+  EXPECT_NEAR(vals[0], 0.5f, 1e-7);
+  EXPECT_NEAR(vals[1], 0.25f, 1e-7);
+}
+TEST(MapStorage, SubAddSubGet) {
+  MapStorage<double> s;
+  s.SubAdd(SArray<Key>({3, 4}), SArray<char>(SArray<double>({0.1, 0.2})));
+  s.SubAdd(SArray<Key>({4}), SArray<char>(SArray<double>({0.3})));
+  SArray<double> v(s.SubGet(SArray<Key>({3, 4})));
+  EXPECT_NEAR(v[0], 0.1, 1e-12);
+  EXPECT_NEAR(v[1], 0.5, 1e-12);
+}
+
+// server/util/pending_buffer_test.cpp:23-60
+TEST(PendingBuffer, Construct) { PendingBuffer b; EXPECT_EQ(b.Size(0), 0); }
+TEST(PendingBuffer, PushAndPop) {
+  PendingBuffer b;
+  Message m1 = Msg(Flag::kGet, 1, 0), m2 = Msg(Flag::kGet, 2, 0), m3 = Msg(Flag::kGet, 3, 0);
+  b.Push(0, m1);
+  b.Push(0, m2);
+  b.Push(1, m3);
+  EXPECT_EQ(b.Size(0), 2);
+  EXPECT_EQ(b.Size(1), 1);
+  auto at0 = b.Pop(0);
+  EXPECT_EQ(at0.size(), 2u);
+  EXPECT_EQ(at0[0].meta.sender, 1);
+  EXPECT_EQ(at0[1].meta.sender, 2);
+  EXPECT_EQ(b.Size(0), 0);
+  EXPECT_EQ(b.Pop(1).size(), 1u);
+  EXPECT_EQ(b.Pop(1).size(), 0u);
+}
+
+// server/util/progress_tracker_test.cpp:21-49
+TEST(ProgressTracker, Basic) {
+  ProgressTracker t;
+  t.Init({1, 2, 3});
+  EXPECT_EQ(t.GetNumThreads(), 3);
+  EXPECT_EQ(t.GetMinClock(), 0);
+  EXPECT_EQ(t.GetProgress(2), 0);
+}
+TEST(ProgressTracker, CheckThreadValid) {
+  ProgressTracker t;
+  t.Init({1, 3});
+  EXPECT_TRUE(t.CheckThreadValid(1));
+  EXPECT_TRUE(!t.CheckThreadValid(2));
+  EXPECT_TRUE(t.CheckThreadValid(3));
+}
+TEST(ProgressTracker, Advance) {
+  ProgressTracker t;
+  t.Init({1, 3});
+  EXPECT_EQ(t.AdvanceAndGetChangedMinClock(1), -1);  // 1:1 3:0
+  EXPECT_EQ(t.AdvanceAndGetChangedMinClock(3), 1);   // 1:1 3:1 -> min 1
+  EXPECT_EQ(t.AdvanceAndGetChangedMinClock(1), -1);  // 1:2
+  EXPECT_EQ(t.AdvanceAndGetChangedMinClock(1), -1);  // 1:3
+  EXPECT_EQ(t.AdvanceAndGetChangedMinClock(3), 2);   // 3:2 -> min 2
+  EXPECT_EQ(t.GetProgress(1), 3);
+  EXPECT_EQ(t.GetProgress(3), 2);
+  EXPECT_EQ(t.GetMinClock(), 2);
+}
+
+// server/server_thread_test.cpp:23-126 — actor dispatch counted by a fake model
+namespace {
+struct FakeModel : AbstractModel {
+  int clock = 0, add = 0, get = 0, reset = 0, dump = 0;
+  void Clock(Message&) override { ++clock; }
+  void Add(Message&) override { ++add; }
+  void Get(Message&) override { ++get; }
+  int GetProgress(int) override { return 0; }
+  void ResetWorker(Message&) override { ++reset; }
+  void Dump(Message&) override { ++dump; }
+  void Restore() override {}
+  void Update(int, const std::vector<Node>&, const Range&) override {}
+};
+}  // namespace
+TEST(ServerThread, Construct) { ServerThread st(0); EXPECT_EQ(st.GetId(), 0u); }
+TEST(ServerThread, RegisterModel) {
+  ServerThread st(0);
+  st.RegisterModel(0, std::unique_ptr<AbstractModel>(new FakeModel));
+  st.RegisterModel(1, std::unique_ptr<AbstractModel>(new FakeModel));
+  EXPECT_TRUE(st.GetModel(0) != nullptr);
+  EXPECT_THROW(st.RegisterModel(1, std::unique_ptr<AbstractModel>(new FakeModel)));
+  EXPECT_THROW(st.GetModel(7));
+}
+static void DispatchCase(Flag flag, int FakeModel::*counter) {
+  ServerThread st(0);
+  auto* f0 = new FakeModel;
+  auto* f1 = new FakeModel;
+  st.RegisterModel(0, std::unique_ptr<AbstractModel>(f0));
+  st.RegisterModel(1, std::unique_ptr<AbstractModel>(f1));
+  st.Start();
+  auto* q = st.GetWorkQueue();
+  q->Push(Msg(flag, 1, 0, 0));
+  q->Push(Msg(flag, 1, 0, 1));
+  q->Push(Msg(flag, 1, 0, 0));
+  q->Push(Msg(flag, 1, 0, 9));  // unknown model: logged and skipped
+  q->Push(Msg(Flag::kExit, 0, 0));
+  st.Stop();
+  EXPECT_EQ(f0->*counter, 2);
+  EXPECT_EQ(f1->*counter, 1);
+}
+TEST(ServerThread, Clock) { DispatchCase(Flag::kClock, &FakeModel::clock); }
+TEST(ServerThread, Add) { DispatchCase(Flag::kAdd, &FakeModel::add); }
+TEST(ServerThread, Get) { DispatchCase(Flag::kGet, &FakeModel::get); }
+TEST(ServerThread, ResetAndCheckpoint) {
+  DispatchCase(Flag::kResetWorkerInModel, &FakeModel::reset);
+  DispatchCase(Flag::kCheckpoint, &FakeModel::dump);
+}
+
+// server/consistency/bsp_model_test.cpp:31-132
+TEST(BSPModel, CheckConstructor) {
+  ThreadsafeQueue<Message> q;
+  BSPModel model(0, std::unique_ptr<AbstractStorage>(new MapStorage<int>()), &q);
+  EXPECT_EQ(model.GetGetPendingSize(), 0);
+}
+TEST(BSPModel, CheckGetAndAdd) {
+  ThreadsafeQueue<Message> q;
+  BSPModel model(0, std::unique_ptr<AbstractStorage>(new MapStorage<int>()), &q);
+  ResetWorkers(&model, &q, {2, 3});
+  Message m0 = GetMsg<int>(2, {1});
+  model.Get(m0);
+  EXPECT_EQ(q.Size(), 1);
+  Message sink;
+  q.WaitAndPop(&sink);
+  Message m1 = AddMsg<int>(2, {1}, {100});
+  model.Add(m1);
+  Message c2 = Msg(Flag::kClock, 2, 0);
+  model.Clock(c2);
+  EXPECT_EQ(model.GetProgress(2), 1);
+  EXPECT_EQ(model.GetProgress(3), 0);
+  EXPECT_EQ(model.GetAddPendingSize(), 1);
+  // worker 3 (still at clock 0) must not see the buffered add
+  Message g3 = GetMsg<int>(3, {1});
+  model.Get(g3);
+  EXPECT_EQ(q.Size(), 1);
+  Message r;
+  q.WaitAndPop(&r);
+  EXPECT_EQ(SArray<int>(r.data[1])[0], 0);
+  // worker 2 is one clock ahead: its get is parked
+  Message g2 = GetMsg<int>(2, {1});
+  model.Get(g2);
+  EXPECT_EQ(model.GetGetPendingSize(), 1);
+  EXPECT_EQ(q.Size(), 0);
+  Message c3 = Msg(Flag::kClock, 3, 0);
+  model.Clock(c3);
+  EXPECT_EQ(model.GetProgress(3), 1);
+  EXPECT_EQ(model.GetAddPendingSize(), 0);
+  EXPECT_EQ(model.GetGetPendingSize(), 0);
+  EXPECT_EQ(q.Size(), 1);  // the parked get was answered at the edge, after the add
+  q.WaitAndPop(&r);
+  EXPECT_EQ(r.meta.recver, 2);
+  EXPECT_EQ(SArray<int>(r.data[1])[0], 100);
+  Message g3b = GetMsg<int>(3, {1});
+  model.Get(g3b);
+  q.WaitAndPop(&r);
+  EXPECT_EQ(SArray<int>(r.data[1])[0], 100);
+}
+
+// server/consistency/ssp_model_test.cpp:33-252
+TEST(SSPModel, CheckConstructor) {
+  ThreadsafeQueue<Message> q;
+  SSPModel model(0, std::unique_ptr<AbstractStorage>(new MapStorage<int>()), 1, &q);
+  EXPECT_EQ(model.GetStaleness(), 1);
+}
+TEST(SSPModel, CheckGetAndAdd) {
+  ThreadsafeQueue<Message> q;
+  SSPModel model(0, std::unique_ptr<AbstractStorage>(new MapStorage<int>()), 1, &q);
+  ResetWorkers(&model, &q, {2, 3});
+  Message a1 = AddMsg<int>(2, {0, 1}, {1, 2});
+  model.Add(a1);  // applied at once
+  Message a2 = AddMsg<int>(3, {1, 2}, {10, 20});
+  model.Add(a2);
+  Message g = GetMsg<int>(3, {0, 1, 2});
+  model.Get(g);
+  Message r;
+  EXPECT_EQ(q.Size(), 1);
+  q.WaitAndPop(&r);
+  SArray<int> v(r.data[1]);
+  EXPECT_EQ(v[0], 1);
+  EXPECT_EQ(v[1], 12);
+  EXPECT_EQ(v[2], 20);
+}
+TEST(SSPModel, CheckClock) {
+  ThreadsafeQueue<Message> q;
+  SSPModel model(0, std::unique_ptr<AbstractStorage>(new MapStorage<int>()), 1, &q);
+  ResetWorkers(&model, &q, {2, 3});
+  Message c = Msg(Flag::kClock, 2, 0);
+  model.Clock(c);
+  EXPECT_EQ(model.GetProgress(2), 1);
+  EXPECT_EQ(model.GetProgress(3), 0);
+  c = Msg(Flag::kClock, 3, 0);
+  model.Clock(c);
+  EXPECT_EQ(model.GetProgress(2), 1);
+  EXPECT_EQ(model.GetProgress(3), 1);
+  c = Msg(Flag::kClock, 2, 0);
+  model.Clock(c);
+  EXPECT_EQ(model.GetProgress(2), 2);
+  EXPECT_EQ(model.GetProgress(3), 1);
+}
+TEST(SSPModel, CheckStaleness) {
+  ThreadsafeQueue<Message> q;
+  SSPModel model(0, std::unique_ptr<AbstractStorage>(new MapStorage<int>()), 2, &q);
+  ResetWorkers(&model, &q, {2, 3});
+  Message g = GetMsg<int>(2, {0});
+  model.Get(g);
+  Message r;
+  q.WaitAndPop(&r);
+  Message c = Msg(Flag::kClock, 2, 0);
+  model.Clock(c);
+  Message a = AddMsg<int>(2, {0}, {1});
+  model.Add(a);
+  c = Msg(Flag::kClock, 2, 0);
+  model.Clock(c);
+  c = Msg(Flag::kClock, 2, 0);
+  model.Clock(c);
+  // worker 2 at clock 3, min 0, staleness 2 -> parked in bucket 3 - 2 = 1
+  g = GetMsg<int>(2, {0});
+  model.Get(g);
+  EXPECT_EQ(model.GetPendingSize(1), 1);
+  EXPECT_EQ(q.Size(), 0);
+  c = Msg(Flag::kClock, 3, 0);
+  model.Clock(c);  // min -> 1 releases the bucket
+  EXPECT_EQ(model.GetPendingSize(1), 0);
+  EXPECT_EQ(q.Size(), 1);
+  q.WaitAndPop(&r);
+  EXPECT_EQ(SArray<int>(r.data[1])[0], 1);
+  g = GetMsg<int>(2, {0});
+  model.Get(g);
+  EXPECT_EQ(model.GetPendingSize(1), 0);
+  EXPECT_EQ(q.Size(), 1);
+}
+
+// server/consistency/asp_model_test.cpp:35-181
+TEST(ASPModel, CheckConstructor) {
+  ThreadsafeQueue<Message> q;
+  ASPModel model(0, std::unique_ptr<AbstractStorage>(new MapStorage<int>()), &q);
+  EXPECT_EQ(q.Size(), 0);
+}
+TEST(ASPModel, CheckGetAndAdd) {
+  ThreadsafeQueue<Message> q;
+  ASPModel model(0, std::unique_ptr<AbstractStorage>(new MapStorage<int>()), &q);
+  ResetWorkers(&model, &q, {2, 3});
+  Message c = Msg(Flag::kClock, 2, 0);
+  for (int i = 0; i < 5; ++i) model.Clock(c);  // worker 2 far ahead: never blocked
+  Message a = AddMsg<int>(2, {7}, {3});
+  model.Add(a);
+  Message g = GetMsg<int>(2, {7});
+  model.Get(g);
+  EXPECT_EQ(q.Size(), 1);
+  Message r;
+  q.WaitAndPop(&r);
+  EXPECT_EQ(SArray<int>(r.data[1])[0], 3);
+  g = GetMsg<int>(3, {7});
+  model.Get(g);
+  q.WaitAndPop(&r);
+  EXPECT_EQ(SArray<int>(r.data[1])[0], 3);
+  EXPECT_EQ(model.GetProgress(2), 5);
+  EXPECT_EQ(model.GetProgress(3), 0);
+  Message bad = GetMsg<int>(9, {7});
+  EXPECT_THROW(model.Get(bad));
+}
+
+// comm/sender_test.cpp:24-76
+namespace {
+struct FakeMailbox : AbstractMailbox {
+  std::vector<Message> sent;
+  std::mutex mu;
+  int Send(const Message& m) override {
+    std::lock_guard<std::mutex> lk(mu);
+    sent.push_back(m);
+    return 0;
+  }
+};
+struct FakeIdMapper : AbstractIdMapper {
+  uint32_t GetNodeIdForThread(uint32_t tid) override { return tid; }  // tid IS the node id
+};
+}  // namespace
+TEST(Sender, StartStop) {
+  FakeMailbox mb;
+  Sender s(&mb);
+  s.Start();
+  s.Stop();
+  EXPECT_EQ(mb.sent.size(), 0u);
+}
+TEST(Sender, Send) {
+  FakeMailbox mb;
+  Sender s(&mb);
+  s.Start();
+  s.GetMessageQueue()->Push(Msg(Flag::kAdd, 1, 2));
+  s.GetMessageQueue()->Push(Msg(Flag::kGet, 3, 4));
+  s.Stop();
+  EXPECT_EQ(mb.sent.size(), 2u);
+  EXPECT_EQ(mb.sent[0].meta.recver, 2);
+  EXPECT_TRUE(mb.sent[1].meta.flag == Flag::kGet);
+}
+
+// comm/mailbox_test.cpp:40-253
+TEST(Mailbox, ConnectAndBind) {
+  Node n{0, "localhost", PortBase()};
+  FakeIdMapper idm;
+  Mailbox mb(n, {n}, &idm);
+  mb.BindAndListen();
+  mb.StartReceiving();
+  mb.ConnectAll();
+  mb.StopReceiving();
+  mb.CloseSockets();
+}
+TEST(Mailbox, StartStop) {
+  Node n{0, "localhost", PortBase() + 1};
+  FakeIdMapper idm;
+  Mailbox mb(n, {n}, &idm);
+  mb.Start();
+  mb.Stop();
+}
+TEST(Mailbox, SendAndRecv) {
+  Node n{0, "localhost", PortBase() + 2};
+  FakeIdMapper idm;
+  Mailbox mb(n, {n}, &idm);
+  ThreadsafeQueue<Message> q;
+  mb.RegisterQueue(0, &q);
+  mb.Start();
+  Message m = Msg(Flag::kAdd, 0, 0, 3);
+  m.AddData(SArray<Key>({4, 5, 6}));
+  m.AddData(SArray<float>({0.4f, 0.2f, 0.3f}));
+  EXPECT_EQ(mb.Send(m), 0);
+  Message r;
+  q.WaitAndPop(&r);
+  EXPECT_TRUE(r.meta.flag == Flag::kAdd);
+  EXPECT_EQ(r.meta.model_id, 3);
+  EXPECT_EQ(r.data.size(), 2u);
+  SArray<Key> k(r.data[0]);
+  SArray<float> v(r.data[1]);
+  EXPECT_EQ(k.size(), 3u);
+  EXPECT_EQ(k[2], 6u);
+  EXPECT_NEAR(v[1], 0.2f, 1e-7);
+  mb.Stop();
+  Message ex;
+  q.WaitAndPop(&ex);  // Stop pushes kExit into every registered queue
+  EXPECT_TRUE(ex.meta.flag == Flag::kExit);
+}
+TEST(Mailbox, Receiving) {
+  Node n{0, "localhost", PortBase() + 3};
+  FakeIdMapper idm;
+  Mailbox mb(n, {n}, &idm);
+  ThreadsafeQueue<Message> q;
+  mb.RegisterQueue(0, &q);
+  EXPECT_EQ(mb.GetQueueMapSize(), 1u);
+  mb.Start();
+  for (int i = 0; i < 100; ++i) mb.Send(Msg(Flag::kClock, i, 0));
+  for (int i = 0; i < 100; ++i) {
+    Message r;
+    q.WaitAndPop(&r);
+    EXPECT_EQ(r.meta.sender, i);  // FIFO per connection
+  }
+  mb.Send(Msg(Flag::kClock, 0, 5));  // unknown receiver: logged, dropped, no crash
+  mb.Stop();
+  mb.DeregisterQueue(0);
+  EXPECT_EQ(mb.GetQueueMapSize(), 0u);
+}
+static void MultiNodeBarrier(int n_nodes, int port0, int rounds, bool also_send) {
+  std::vector<Node> nodes;
+  for (int i = 0; i < n_nodes; ++i) nodes.push_back(Node{static_cast<uint32_t>(i), "localhost", port0 + i});
+  std::vector<std::thread> ths;
+  std::atomic<int> ok{0};
+  for (int i = 0; i < n_nodes; ++i)
+    ths.emplace_back([&, i] {
+      FakeIdMapper idm;
+      Mailbox mb(nodes[i], nodes, &idm);
+      ThreadsafeQueue<Message> q;
+      mb.RegisterQueue(static_cast<uint32_t>(i), &q);
+      mb.Start();
+      for (int r = 0; r < rounds; ++r) mb.Barrier();
+      if (also_send) {
+        const int peer = (i + 1) % n_nodes;
+        Message m = Msg(Flag::kGet, i, peer);
+        m.AddData(SArray<Key>({static_cast<Key>(i)}));
+        mb.Send(m);
+        Message r;
+        q.WaitAndPop(&r);
+        if (r.meta.sender == (i + n_nodes - 1) % n_nodes && SArray<Key>(r.data[0])[0] == static_cast<Key>(r.meta.sender)) ++ok;
+      } else {
+        ++ok;
+      }
+      mb.Stop();
+    });
+  for (auto& t : ths) t.join();
+  EXPECT_EQ(ok.load(), n_nodes);
+}
+TEST(Mailbox, SendRecvTwoNodes) { MultiNodeBarrier(2, PortBase() + 4, 1, true); }
+TEST(Mailbox, ReceivingTwoNodes) { MultiNodeBarrier(2, PortBase() + 6, 0, true); }
+TEST(Mailbox, BarrierTwoNodes) { MultiNodeBarrier(2, PortBase() + 8, 10, false); }
+TEST(Mailbox, BarrierFourNodes) { MultiNodeBarrier(4, PortBase() + 10, 10, false); }
+
+// worker/kv_client_table_test.cpp:20-238
+namespace {
+struct FakePartitionManager : AbstractPartitionManager {
+  Key split;
+  FakePartitionManager(const std::vector<uint32_t>& tids, Key s) : AbstractPartitionManager(tids), split(s) {}
+  void Slice(const Keys& keys, std::vector<std::pair<int, Keys>>* sliced) const override {
+    sliced->clear();
+    size_t n = 0;
+    while (n < keys.size() && keys[n] < split) ++n;
+    if (n) sliced->emplace_back(server_thread_ids_[0], keys.segment(0, n));
+    if (n < keys.size()) sliced->emplace_back(server_thread_ids_[1], keys.segment(n, keys.size()));
+  }
+  void Slice(const KVPairs& kvs, std::vector<std::pair<int, KVPairs>>* sliced) const override {
+    sliced->clear();
+    size_t n = 0;
+    while (n < kvs.first.size() && kvs.first[n] < split) ++n;
+    if (n) sliced->emplace_back(server_thread_ids_[0], KVPairs(kvs.first.segment(0, n), kvs.second.segment(0, n)));
+    if (n < kvs.first.size())
+      sliced->emplace_back(server_thread_ids_[1], KVPairs(kvs.first.segment(n, kvs.first.size()),
+                                                          kvs.second.segment(n, kvs.second.size())));
+  }
+  void Update(const std::vector<Range>&, const std::vector<uint32_t>&) override {}
+};
+struct FakeCallbackRunner : AbstractCallbackRunner {
+  std::function<void(Message&)> recv;
+  std::function<void()> finish;
+  std::mutex mu;
+  std::condition_variable cv;
+  uint32_t expected = 0, current = 0;
+  void RegisterRecvHandle(uint32_t, uint32_t, const std::function<void(Message&)>& h) override { recv = h; }
+  void RegisterRecvFinishHandle(uint32_t, uint32_t, const std::function<void()>& h) override { finish = h; }
+  void NewRequest(uint32_t, uint32_t, uint32_t e) override {
+    std::lock_guard<std::mutex> lk(mu);
+    expected = e;
+    current = 0;
+  }
+  void WaitRequest(uint32_t, uint32_t) override {
+    std::unique_lock<std::mutex> lk(mu);
+    cv.wait(lk, [this] { return current >= expected; });
+  }
+  void AddResponse(uint32_t, uint32_t, Message& m) override {
+    recv(m);
+    bool last;
+    {
+      std::lock_guard<std::mutex> lk(mu);
+      last = current + 1 == expected;
+    }
+    if (last) finish();
+    {
+      std::lock_guard<std::mutex> lk(mu);
+      ++current;
+    }
+    cv.notify_all();
+  }
+  void NewCheckPoint(uint32_t, uint32_t, uint32_t) override {}
+  void WaitCheckPoint(uint32_t, uint32_t) override {}
+  void CheckPointResponse(uint32_t, uint32_t) override {}
+};
+}  // namespace
+TEST(KVClientTable, Init) {
+  ThreadsafeQueue<Message> q;
+  FakePartitionManager pm({0, 1}, 4);
+  FakeCallbackRunner cr;
+  KVClientTable<double> table(100, 0, &q, &pm, &cr);
+  EXPECT_TRUE(static_cast<bool>(cr.recv));
+}
+TEST(KVClientTable, Add) {
+  ThreadsafeQueue<Message> q;
+  FakePartitionManager pm({0, 1}, 4);
+  FakeCallbackRunner cr;
+  KVClientTable<double> table(100, 7, &q, &pm, &cr);
+  table.Add(std::vector<Key>({3, 4, 5, 6}), std::vector<double>({0.1, 0.1, 0.1, 0.1}));
+  EXPECT_EQ(q.Size(), 2);
+  Message m1, m2;
+  q.WaitAndPop(&m1);
+  q.WaitAndPop(&m2);
+  EXPECT_EQ(m1.meta.sender, 100);
+  EXPECT_EQ(m1.meta.recver, 0);
+  EXPECT_EQ(m1.meta.model_id, 7);
+  EXPECT_TRUE(m1.meta.flag == Flag::kAdd);
+  EXPECT_EQ(SArray<Key>(m1.data[0]).size(), 1u);
+  EXPECT_EQ(SArray<Key>(m1.data[0])[0], 3u);
+  EXPECT_EQ(m2.meta.recver, 1);
+  EXPECT_EQ(SArray<Key>(m2.data[0]).size(), 3u);
+  EXPECT_EQ(SArray<double>(m2.data[1]).size(), 3u);
+  table.Clock();
+  EXPECT_EQ(q.Size(), 2);  // kClock goes to every server of the table
+}
+TEST(KVClientTable, Get) {
+  ThreadsafeQueue<Message> q;
+  FakePartitionManager pm({0, 1}, 4);
+  FakeCallbackRunner cr;
+  KVClientTable<double> table(100, 0, &q, &pm, &cr);
+  std::vector<double> vals;
+  std::thread user([&] { table.Get(std::vector<Key>({3, 4, 5, 6}), &vals); });
+  Message r1, r2;
+  q.WaitAndPop(&r1);
+  q.WaitAndPop(&r2);
+  EXPECT_TRUE(r1.meta.flag == Flag::kGet);
+  EXPECT_EQ(SArray<Key>(r1.data[0]).size(), 1u);
+  EXPECT_EQ(SArray<Key>(r2.data[0]).size(), 3u);
+  // replies arrive out of order: the table re-orders by first key
+  Message a2 = Msg(Flag::kGet, 1, 100);
+  a2.AddData(SArray<Key>({4, 5, 6}));
+  a2.AddData(SArray<double>({0.4, 0.2, 0.3}));
+  Message a1 = Msg(Flag::kGet, 0, 100);
+  a1.AddData(SArray<Key>({3}));
+  a1.AddData(SArray<double>({0.1}));
+  cr.AddResponse(100, 0, a2);
+  cr.AddResponse(100, 0, a1);
+  user.join();
+  EXPECT_EQ(vals.size(), 4u);
+  EXPECT_NEAR(vals[0], 0.1, 1e-12);
+  EXPECT_NEAR(vals[1], 0.4, 1e-12);
+  EXPECT_NEAR(vals[2], 0.2, 1e-12);
+  EXPECT_NEAR(vals[3], 0.3, 1e-12);
+}
+
+// driver/engine_test.cpp:30-157
+TEST(Engine, Construct) {
+  Node n{0, "localhost", PortBase() + 14};
+  Engine e(n, {n});
+  EXPECT_EQ(e.GetNodes().size(), 1u);
+}
+TEST(Engine, StartMailbox) {
+  Node n{0, "localhost", PortBase() + 14};
+  Engine e(n, {n});
+  e.CreateIdMapper();
+  e.CreateMailbox();
+  e.StartMailbox();
+  e.StopMailbox();
+}
+TEST(Engine, StartEverything) {
+  Node n{0, "localhost", PortBase() + 14};
+  Engine e(n, {n});
+  e.StartEverything();
+  e.StopEverything();
+}
+static void ThreeEngines(int port0, const std::function<void(Engine&, const std::vector<Node>&)>& body) {
+  std::vector<Node> nodes{{0, "localhost", port0}, {1, "localhost", port0 + 1}, {2, "localhost", port0 + 2}};
+  std::vector<std::thread> ths;
+  std::vector<std::string> errs;
+  std::mutex mu;
+  for (const auto& node : nodes)
+    ths.emplace_back([&, node] {
+      try {
+        Engine e(node, nodes);
+        e.StartEverything();
+        body(e, nodes);
+        e.StopEverything();
+      } catch (const std::exception& ex) {
+        std::lock_guard<std::mutex> lk(mu);
+        errs.push_back(ex.what());
+      }
+    });
+  for (auto& t : ths) t.join();
+  EXPECT_TRUE(errs.empty());
+  for (auto& e : errs) std::cerr << "    engine error: " << e << "\n";
+}
+TEST(Engine, MultipleStartEverything) {
+  ThreeEngines(PortBase() + 15, [](Engine&, const std::vector<Node>&) {});
+}
+TEST(Engine, SimpleTaskMapStorage) {
+  Node n{0, "localhost", PortBase() + 14};
+  Engine e(n, {n});
+  e.StartEverything();
+  const uint32_t tid = e.CreateTable<double>({{0, 10}}, ModelType::SSP, StorageType::Map, 1);
+  e.Barrier();
+  MLTask task;
+  task.SetWorkerAlloc({{0, 3}});
+  task.SetTables({tid});
+  std::atomic<int> ran{0};
+  task.SetLambda([&](const Info& info) {
+    EXPECT_TRUE(info.thread_id >= 100 && info.thread_id < 103);
+    EXPECT_TRUE(info.worker_id < 3);
+    ++ran;
+  });
+  e.Run(task);
+  EXPECT_EQ(ran.load(), 3);
+  e.StopEverything();
+}
+TEST(Engine, MultipleTasks) {
+  std::atomic<int> ran{0};
+  ThreeEngines(PortBase() + 15, [&](Engine& e, const std::vector<Node>&) {
+    const uint32_t tid = e.CreateTable<double>({{0, 10}, {10, 20}, {20, 30}}, ModelType::SSP, StorageType::Map, 1);
+    e.Barrier();
+    MLTask task;
+    task.SetWorkerAlloc({{0, 3}, {1, 2}, {2, 3}});
+    task.SetTables({tid});
+    task.SetLambda([&](const Info&) { ++ran; });
+    e.Run(task);
+  });
+  EXPECT_EQ(ran.load(), 8);
+}
+TEST(Engine, KVClientTableMapStorage) {
+  for (auto storage : {StorageType::Map, StorageType::Vector}) {
+    Node n{0, "localhost", PortBase() + 14};
+    Engine e(n, {n});
+    e.StartEverything();
+    const uint32_t tid = e.CreateTable<double>({{0, 10}}, ModelType::SSP, storage, 1);
+    e.Barrier();
+    MLTask task;
+    task.SetWorkerAlloc({{0, 2}});
+    task.SetTables({tid});
+    std::vector<std::vector<double>> finals(2);
+    task.SetLambda([&](const Info& info) {
+      auto table = info.CreateKVClientTable<double>(tid);
+      std::vector<Key> keys{3, 4, 5, 6};
+      for (int i = 0; i < 10; ++i) {
+        std::vector<double> vals;
+        table->Get(keys, &vals);
+        EXPECT_EQ(vals.size(), 4u);
+        table->Add(keys, {0.5, 0.5, 0.5, 0.5});
+        table->Clock();
+      }
+      table->Get(keys, &finals[info.worker_id]);
+    });
+    e.Run(task);
+    // after the closing barrier every add has landed
+    MLTask check;
+    check.SetWorkerAlloc({{0, 1}});
+    check.SetTables({tid});
+    check.SetLambda([&](const Info& info) {
+      auto table = info.CreateKVClientTable<double>(tid);
+      std::vector<double> vals;
+      table->Get({3, 4, 5, 6}, &vals);
+      for (double v : vals) EXPECT_NEAR(v, 10.0, 1e-12);
+    });
+    e.Run(check);
+    e.StopEverything();
+  }
+}
+
+// ================================================================== part 2: beyond the reference's tests
+TEST(SArray, ZeroCopyViewsAndGrowth) {
+  SArray<int> a({1, 2, 3, 4});
+  SArray<char> bytes(a);
+  EXPECT_EQ(bytes.size(), 16u);
+  SArray<int> back(bytes);
+  back[0] = 9;
+  EXPECT_EQ(a[0], 9);  // same storage
+  SArray<int> seg = a.segment(1, 3);
+  EXPECT_EQ(seg.size(), 2u);
+  seg[0] = 7;
+  EXPECT_EQ(a[1], 7);
+  SArray<int> g;
+  for (int i = 0; i < 100; ++i) g.push_back(i);
+  EXPECT_EQ(g.size(), 100u);
+  EXPECT_EQ(g[99], 99);
+  g.resize(3);
+  g.resize(6, -1);
+  EXPECT_EQ(g[2], 2);
+  EXPECT_EQ(g[5], -1);  // regrown elements take the init value (reference quirk 2.8-2 not reproduced)
+  SArray<int> c;
+  c.CopyFrom(a);
+  c[0] = 0;
+  EXPECT_EQ(a[0], 9);
+  g.append(a);
+  EXPECT_EQ(g.size(), 10u);
+  SArray<Key> sorted({1, 3, 5, 7, 9});
+  Range r = FindRange<Key>(sorted, 3, 8);
+  EXPECT_EQ(r.begin(), 1u);
+  EXPECT_EQ(r.end(), 4u);
+  EXPECT_THROW(a.segment(3, 9));
+}
+TEST(BinStream, RoundTrips) {
+  BinStream s;
+  std::map<std::string, std::vector<int>> m{{"a", {1, 2}}, {"b", {}}};
+  std::vector<bool> bits{true, false, true};
+  s << 42 << 2.5 << std::string("hello") << m << bits << std::make_pair(7, std::string("x")) << SArray<float>({1.f, 2.f});
+  BinStream inner;
+  inner << 1 << 2;
+  s << inner;
+  int i = 0;
+  double d = 0;
+  std::string str;
+  std::map<std::string, std::vector<int>> m2;
+  std::vector<bool> bits2;
+  std::pair<int, std::string> p;
+  SArray<float> arr;
+  BinStream inner2;
+  s >> i >> d >> str >> m2 >> bits2 >> p >> arr >> inner2;
+  EXPECT_EQ(i, 42);
+  EXPECT_NEAR(d, 2.5, 0);
+  EXPECT_EQ(str, std::string("hello"));
+  EXPECT_TRUE(m2 == m);
+  EXPECT_TRUE(bits2 == bits);
+  EXPECT_EQ(p.second, std::string("x"));
+  EXPECT_EQ(arr.size(), 2u);
+  EXPECT_EQ(inner2.size(), 8u);
+  EXPECT_EQ(s.size(), 0u);
+  EXPECT_THROW(s >> i);
+}
+TEST(ThreadsafeQueue, BlockingAndTimed) {
+  ThreadsafeQueue<int> q;
+  int v = 0;
+  EXPECT_TRUE(!q.TryPop(&v));
+  EXPECT_TRUE(!q.WaitAndPopFor(&v, 10));
+  std::thread t([&] {
+    std::this_thread::sleep_for(std::chrono::milliseconds(20));
+    q.Push(5);
+  });
+  q.WaitAndPop(&v);
+  t.join();
+  EXPECT_EQ(v, 5);
+}
+TEST(Context, FlagsAndIterationMap) {
+  Flags::Get().Reset();
+  Context::get_instance().clear();
+  Flags::Get().Define("num_dims", "123");
+  Flags::Get().Define("scale", "false");
+  Flags::Get().Define("alpha", "0.1");
+  auto pos = Flags::Get().Parse(std::vector<std::string>{"--num_dims=456", "--config_file", "cfg", "--scale", "pos", "--my_id=2"});
+  auto& ctx = Context::get_instance();
+  EXPECT_EQ(ctx.get_int32("num_dims"), 456);
+  EXPECT_EQ(ctx.get_string("config_file"), std::string("cfg"));
+  EXPECT_TRUE(ctx.get_bool("scale"));
+  EXPECT_EQ(pos.size(), 1u);
+  EXPECT_NEAR(ctx.get_double("alpha"), 0.1, 1e-12);
+  EXPECT_EQ(ctx.get_int32("missing"), 0);
+  EXPECT_TRUE(!ctx.get_bool("missing"));
+  ctx.set("scale", false);
+  EXPECT_TRUE(!ctx.get_bool("scale"));
+  ctx.set_iteration(3, 200);
+  EXPECT_EQ(ctx.get_iteration(3), 200);
+  EXPECT_EQ(ctx.get_iteration(4), 0);
+  Flags::Get().Reset();
+  ctx.clear();
+}
+TEST(NodeUtils, ParseSelectCheck) {
+  auto nodes = ParseLines("0:localhost:14560\n# comment\n1:localhost:14561\n\n2:worker-7:14562\n");
+  EXPECT_EQ(nodes.size(), 3u);
+  EXPECT_EQ(nodes[2].hostname, std::string("worker-7"));
+  EXPECT_EQ(nodes[2].port, 14562);
+  EXPECT_TRUE(CheckValidNodeIds(nodes));
+  EXPECT_TRUE(CheckUniquePort(nodes));
+  EXPECT_TRUE(CheckConsecutiveIds(nodes));
+  EXPECT_TRUE(HasNode(nodes, 1));
+  EXPECT_EQ(GetNodeById(nodes, 2).port, 14562);
+  EXPECT_THROW(GetNodeById(nodes, 9));
+  auto copy = nodes;
+  Node none = SelectMaster(copy, -1);
+  EXPECT_TRUE(!none.is_master);
+  EXPECT_EQ(copy.size(), 3u);
+  Node master = SelectMaster(copy, 10);  // node 1 leaves the worker set and becomes master
+  EXPECT_TRUE(master.is_master);
+  EXPECT_EQ(master.id, 1u);
+  EXPECT_EQ(copy.size(), 2u);
+  EXPECT_TRUE(!CheckConsecutiveIds(copy));
+  EXPECT_THROW(ParseLines("garbage"));
+  const std::string f = TmpDir() + "hostfile";
+  { std::ofstream(f) << "0:a:1\n1:b:2\n"; }
+  EXPECT_EQ(ParseFile(f).size(), 2u);
+}
+TEST(FileIo, HdfsPathsMapToLocalRoot) {
+  ::setenv("MINIPS_HDFS_ROOT", (TmpDir() + "hdfs").c_str(), 1);
+  EXPECT_TRUE(io::IsHdfsPath("hdfs://proj10:9000/ybai/dump_"));
+  EXPECT_EQ(io::ResolvePath("hdfs://proj10:9000/ybai/dump_"), TmpDir() + "hdfs/ybai/dump_");
+  EXPECT_EQ(io::ResolvePath("hdfs:///a/b"), TmpDir() + "hdfs/a/b");
+  EXPECT_EQ(io::ResolvePath("/plain/path"), std::string("/plain/path"));
+  {
+    io::ofstream out("hdfs:///dir/file.txt");
+    EXPECT_TRUE(out.is_open());
+    out << "hello";
+  }
+  io::ifstream in("hdfs://nn:9000/dir/file.txt");
+  std::string s;
+  in >> s;
+  EXPECT_EQ(s, std::string("hello"));
+  EXPECT_TRUE(io::Exists("hdfs:///dir/file.txt"));
+  EXPECT_EQ(io::FileSize("hdfs:///dir/file.txt"), 5);
+}
+TEST(VectorStorage, AddGetBoundsAndDumpFormat) {
+  Context::get_instance().clear();
+  VectorStorage<double> s(Range(10, 20));
+  s.SubAdd(SArray<Key>({10, 13, 19}), SArray<char>(SArray<double>({1.5, -2.25, 1e-9})));
+  s.SubAdd(SArray<Key>({13}), SArray<char>(SArray<double>({0.25})));
+  SArray<double> v(s.SubGet(SArray<Key>({10, 11, 13, 19})));
+  EXPECT_NEAR(v[0], 1.5, 0);
+  EXPECT_NEAR(v[1], 0.0, 0);
+  EXPECT_NEAR(v[2], -2.0, 0);
+  EXPECT_THROW(s.SubGet(SArray<Key>({20})));
+  EXPECT_THROW(s.SubAdd(SArray<Key>({9}), SArray<char>(SArray<double>({1.0}))));
+  const std::string path = TmpDir() + "server_params_0";
+  s.DumpTo(path);
+  std::ifstream in(path);
+  std::string content((std::istreambuf_iterator<char>(in)), std::istreambuf_iterator<char>());
+  // one line, "<local_idx>:<val> " per non-zero entry, local index = key - range.begin
+  EXPECT_TRUE(content.rfind("0:1.5 3:-2 9:", 0) == 0);
+  EXPECT_TRUE(content.find('\n') == std::string::npos);
+  VectorStorage<double> r(Range(10, 20));
+  r.RestoreFrom(path);
+  SArray<double> rv(r.SubGet(SArray<Key>({10, 11, 13, 19})));
+  for (int i = 0; i < 4; ++i) EXPECT_NEAR(rv[i], v[i], 0);  // exact round trip (the reference truncates to int)
+  // toggle-gated paths
+  auto& ctx = Context::get_instance();
+  ctx.set("checkpoint_toggle", true);
+  ctx.set("checkpoint_file_prefix", TmpDir() + "ck_");
+  ctx.set("my_id", 3);
+  s.Dump();
+  EXPECT_TRUE(io::Exists(TmpDir() + "ck_server_params_3"));
+  ctx.clear();
+}
+TEST(ProgressTracker, DeleteNodeDumpRestore) {
+  Context::get_instance().clear();
+  ProgressTracker t;
+  t.Init({100, 101, 1100});
+  t.AdvanceAndGetChangedMinClock(100);
+  t.AdvanceAndGetChangedMinClock(101);
+  EXPECT_EQ(t.GetMinClock(), 0);
+  EXPECT_EQ(t.DeleteNode(1), 1);  // the straggler's node disappears: min moves
+  EXPECT_EQ(t.GetNumThreads(), 2);
+  for (int i = 0; i < 99; ++i) {
+    t.AdvanceAndGetChangedMinClock(100);
+    t.AdvanceAndGetChangedMinClock(101);
+  }
+  t.AdvanceAndGetChangedMinClock(100);  // 100:101 101:100
+  const std::string path = TmpDir() + "server_progress_0";
+  t.DumpTo(path);
+  std::ifstream in(path);
+  std::string content((std::istreambuf_iterator<char>(in)), std::istreambuf_iterator<char>());
+  EXPECT_EQ(content, std::string("min_clock:100 100:100 101:100 "));  // rounded to the checkpoint interval
+  ProgressTracker r;
+  r.Init({100, 101});
+  r.RestoreFrom(path);
+  EXPECT_EQ(r.GetMinClock(), 100);
+  EXPECT_EQ(r.GetProgress(101), 100);
+}
+TEST(Models, CheckpointAcksUnderEveryModelAndRestores) {
+  auto& ctx = Context::get_instance();
+  ctx.clear();
+  ctx.set("checkpoint_toggle", true);
+  ctx.set("checkpoint_file_prefix", TmpDir() + "m_");
+  ctx.set("my_id", 0);
+  for (int kind = 0; kind < 3; ++kind) {
+    ThreadsafeQueue<Message> q;
+    std::unique_ptr<AbstractStorage> st(new VectorStorage<double>(Range(0, 8)));
+    std::unique_ptr<ModelBase> model;
+    if (kind == 0) model.reset(new BSPModel(0, std::move(st), &q));
+    else if (kind == 1) model.reset(new SSPModel(0, std::move(st), 1, &q));
+    else model.reset(new ASPModel(0, std::move(st), &q));
+    ResetWorkers(model.get(), &q, {100});
+    Message a = Msg(Flag::kAdd, 100, 0);
+    a.AddData(SArray<Key>({1, 2}));
+    a.AddData(SArray<double>({0.5, 0.75}));
+    model->Add(a);
+    Message c = Msg(Flag::kClock, 100, 0);
+    model->Clock(c);
+    Message ck = Msg(Flag::kCheckpoint, 100, 0);
+    model->Dump(ck);
+    Message ack;
+    EXPECT_EQ(q.Size(), 1);  // the reference's BSP / ASP never ack
+    q.WaitAndPop(&ack);
+    EXPECT_TRUE(ack.meta.flag == Flag::kCheckpoint);
+    EXPECT_EQ(ack.meta.recver, 100);
+    // diverge, then roll back
+    model->Add(a);
+    model->Clock(c);
+    model->Restore();
+    Message g = Msg(Flag::kGet, 100, 0);
+    g.AddData(SArray<Key>({1, 2}));
+    model->Get(g);
+    Message r;
+    q.WaitAndPop(&r);
+    EXPECT_NEAR(SArray<double>(r.data[1])[0], 0.5, 0);
+    EXPECT_NEAR(SArray<double>(r.data[1])[1], 0.75, 0);
+  }
+  ctx.clear();
+}
+TEST(WorkerThread, ResponsesCheckpointAndRollback) {
+  WorkerThread wt(50);
+  wt.Start();
+  int received = 0, finished = 0;
+  wt.RegisterRecvHandle(100, 0, [&](Message&) { ++received; });
+  wt.RegisterRecvFinishHandle(100, 0, [&] { ++finished; });
+  wt.NewRequest(100, 0, 2);
+  wt.GetWorkQueue()->Push(Msg(Flag::kGet, 0, 100, 0));
+  wt.GetWorkQueue()->Push(Msg(Flag::kGet, 1, 100, 0));
+  wt.WaitRequest(100, 0);
+  EXPECT_EQ(received, 2);
+  EXPECT_EQ(finished, 1);
+  wt.NewCheckPoint(100, 0, 1);
+  wt.GetWorkQueue()->Push(Msg(Flag::kCheckpoint, 0, 100, 0));
+  wt.WaitCheckPoint(100, 0);
+  // a blocked request is released by rollback
+  wt.NewRequest(100, 0, 3);
+  std::thread blocked([&] { wt.WaitRequest(100, 0); });
+  std::this_thread::sleep_for(std::chrono::milliseconds(20));
+  wt.RollBackWorker();
+  blocked.join();
+  wt.GetWorkQueue()->Push(Msg(Flag::kExit, 0, 0));
+  wt.Stop();
+}
+TEST(Engine, BSPAndASPTablesAndCheckpointThroughTheStack) {
+  auto& ctx = Context::get_instance();
+  ctx.clear();
+  ctx.set("checkpoint_toggle", true);
+  ctx.set("checkpoint_file_prefix", TmpDir() + "e_");
+  ctx.set("my_id", 0);
+  Node n{0, "localhost", PortBase() + 14};
+  Engine e(n, {n});
+  e.StartEverything(2);  // two server threads: [0,5) and [5,10)
+  int dumped = 0;
+  e.SetDumpCallback([&] { ++dumped; });
+  const uint32_t bsp = e.CreateTable<double>({{0, 5}, {5, 10}}, ModelType::BSP, StorageType::Vector);
+  const uint32_t asp = e.CreateTable<double>({{0, 5}, {5, 10}}, ModelType::ASP, StorageType::Map);
+  e.Barrier();
+  MLTask task;
+  task.SetWorkerAlloc({{0, 2}});
+  task.SetTables({bsp, asp});
+  task.SetLambda([&](const Info& info) {
+    auto t1 = info.CreateKVClientTable<double>(bsp);
+    auto t2 = info.CreateKVClientTable<double>(asp);
+    std::vector<Key> keys{1, 4, 5, 9};
+    for (int i = 0; i < 5; ++i) {
+      std::vector<double> v;
+      t1->Get(keys, &v);
+      for (double x : v) EXPECT_NEAR(x, 2.0 * i, 1e-12);  // BSP: both workers' adds of earlier clocks, none of this one
+      t1->Add(keys, {1, 1, 1, 1});
+      t1->Clock();
+      t2->Add(keys, {1, 1, 1, 1});
+      t2->Clock();
+    }
+    if (info.worker_id == 0) t1->CheckPoint();  // returns under BSP (hangs in the reference)
+  });
+  e.Run(task);
+  EXPECT_TRUE(dumped >= 2);  // one request per server thread
+  EXPECT_TRUE(io::Exists(TmpDir() + "e_server_params_0"));
+  EXPECT_TRUE(io::Exists(TmpDir() + "e_server_progress_0"));
+  e.StopEverything();
+  ctx.clear();
+}
+TEST(Engine, ForceQuitShrinksTheBarrier) {
+  const int port0 = PortBase() + 15;
+  std::vector<Node> nodes{{0, "localhost", port0}, {1, "localhost", port0 + 1}, {2, "localhost", port0 + 2}};
+  std::vector<std::thread> ths;
+  std::atomic<int> done{0};
+  for (const auto& node : nodes)
+    ths.emplace_back([&, node] {
+      Engine e(node, nodes);
+      e.StartEverything();
+      e.Barrier();
+      if (node.id == 2) {
+        e.ForceQuit();  // no local data: leave before training (lr_example.cpp:145-152)
+        e.GetMailbox()->Stop(false);
+        e.StopSender();
+        ++done;
+        return;
+      }
+      std::this_thread::sleep_for(std::chrono::milliseconds(100));
+      e.Barrier();  // completes with the two remaining nodes
+      EXPECT_EQ(e.GetNodes().size(), 2u);
+      e.StopEverything();
+      ++done;
+    });
+  for (auto& t : ths) t.join();
+  EXPECT_EQ(done.load(), 3);
+}
+TEST(Master, HeartbeatDetectionAndRollbackBroadcast) {
+  MasterThread mt(1, nullptr);
+  std::vector<Node> nodes{{0, "localhost", 1}, {2, "localhost", 2}};
+  mt.Init(nodes);
+  std::vector<std::string> launched;
+  HeartBeatCheckThread hb(&mt, 5, "relaunch.sh", [&](const std::string& cmd) {
+    launched.push_back(cmd);
+    return 0;
+  });
+  const time_t now = std::time(nullptr);
+  EXPECT_EQ(hb.CheckOnce(now + 10).size(), 0u);  // within 3 x interval
+  Message beat = Msg(Flag::kHeartBeat, 0, 1);
+  mt.Handle(beat);
+  auto failed = hb.CheckOnce(now + 16);  // silent for > 15 s
+  EXPECT_EQ(failed.size(), 1u);
+  EXPECT_EQ(launched.size(), 1u);
+  EXPECT_TRUE(launched[0].rfind("relaunch.sh ", 0) == 0);
+  EXPECT_TRUE(mt.GetRecoveringNodeId() >= 0);
+  EXPECT_EQ(hb.CheckOnce(now + 30).size(), 0u);  // one recovery at a time
+  Message q0 = Msg(Flag::kQuitHeartBeat, 0, 1), q2 = Msg(Flag::kQuitHeartBeat, 2, 1);
+  mt.Handle(q0);
+  EXPECT_TRUE(!mt.AllQuit());
+  mt.Handle(q2);
+  EXPECT_TRUE(mt.AllQuit());
+}
+TEST(Master, EndToEndHeartbeatRollback) {
+  auto& ctx = Context::get_instance();
+  ctx.clear();
+  ctx.set("heartbeat_interval", 1);
+  ctx.set("checkpoint_toggle", true);
+  ctx.set("checkpoint_file_prefix", TmpDir() + "hb_");
+  ctx.set("my_id", 0);
+  checkpoint::DumpConfigData({{0, 300}});
+  const int port0 = PortBase() + 15;
+  Node worker{0, "localhost", port0}, master{1, "localhost", port0 + 1};
+  master.is_master = true;
+  Master m(master, {worker});
+  std::thread mth([&] { m.StartMaster(); });
+  Engine e(worker, {worker}, master);
+  e.StartEverything();
+  mth.join();
+  // wait for a heartbeat to reach the master, then let the master order a rollback
+  for (int i = 0; i < 50 && m.GetMasterThread()->GetHeartBeats().empty(); ++i)
+    std::this_thread::sleep_for(std::chrono::milliseconds(50));
+  m.RollBack(0);
+  for (int i = 0; i < 100 && !e.IsNeedRollBack(); ++i) std::this_thread::sleep_for(std::chrono::milliseconds(20));
+  EXPECT_TRUE(e.IsNeedRollBack());
+  EXPECT_EQ(e.GetRollBackIteration(), 300);
+  EXPECT_EQ(ctx.get_iteration(0), 300);
+  e.RecoverEnd();
+  EXPECT_TRUE(!e.IsNeedRollBack());
+  e.StopEverything();  // sends kQuitHeartBeat
+  m.StopMaster();      // returns once every node quit
+  ctx.clear();
+}
+static std::string WriteLibsvm(const std::string& path, int rows) {
+  std::ofstream out(path);
+  for (int r = 0; r < rows; ++r) {
+    out << (r % 2 ? "+1" : "-1");
+    for (int j = 0; j < 1 + r % 5; ++j) out << " " << (1 + (r * 7 + j * 13) % 97) << ":" << (0.5 + j);
+    out << "\n";
+  }
+  return path;
+}
+TEST(Lib, ParseLibsvm) {
+  SVMItem item;
+  EXPECT_TRUE(lib::Parser::parse_libsvm("-1 3:1 11:0.5\t40:2e-1", &item));
+  EXPECT_NEAR(item.second, -1.0, 0);
+  EXPECT_EQ(item.first.size(), 3u);
+  EXPECT_EQ(item.first[0].first, 2);  // 1-based in the file, 0-based in memory
+  EXPECT_NEAR(item.first[2].second, 0.2, 1e-12);
+  EXPECT_TRUE(!lib::Parser::parse_libsvm("", &item));
+  EXPECT_TRUE(!lib::Parser::parse_libsvm("# c", &item));
+  EXPECT_TRUE(lib::Parser::parse_libsvm("1", &item));
+  EXPECT_EQ(item.first.size(), 0u);
+}
+TEST(Lib, BatchDataSamplerKeysAndWrapAround) {
+  std::vector<SVMItem> data{{{{5, 1.0}, {2, 1.0}}, 1}, {{{2, 1.0}, {9, 1.0}}, 0}, {{{0, 1.0}}, 1}};
+  lib::BatchDataSampler<SVMItem> s(data, 2, 1);
+  s.set_start_point(2);
+  SArray<Key> keys = s.prepare_next_batch();  // rows 2 and 0 (wrap-around)
+  EXPECT_EQ(keys.size(), 3u);
+  EXPECT_EQ(keys[0], 0u);
+  EXPECT_EQ(keys[1], 2u);
+  EXPECT_EQ(keys[2], 5u);
+  EXPECT_NEAR(s.get_data_ptrs()[1]->second, 1.0, 0);
+  keys = s.prepare_next_batch();  // rows 1 and 2
+  EXPECT_EQ(keys.size(), 3u);
+  EXPECT_EQ(keys[2], 9u);
+  s.random_start_point();
+  EXPECT_EQ(s.prepare_next_batch().size() > 0, true);
+}
+TEST(Lib, SVMDumperRoundTrips) {
+  std::vector<SVMItem> data{{{{0, 1.5}, {7, -2.0}}, 1}, {{}, 0}, {{{3, 0.125}}, 1}};
+  const std::string p = TmpDir() + "worker_0";
+  lib::SVMDumper::DumpSVMData(data, p);
+  auto back = lib::SVMDumper::LoadSVMData(p);
+  EXPECT_EQ(back.size(), 3u);
+  EXPECT_EQ(back[0].first[1].first, 7);  // indices survive (the reference shifts them by one, 2.8-5)
+  EXPECT_NEAR(back[0].first[1].second, -2.0, 0);
+  EXPECT_EQ(back[1].first.size(), 0u);
+  lib::SVMDumper::DumpConfigData({{0, 149}, {1, 151}}, TmpDir() + "worker_config_0");
+  auto cfg = lib::SVMDumper::LoadConfigData(TmpDir() + "worker_config_0");
+  EXPECT_EQ(cfg[0], 100);  // rounded to the checkpoint interval
+  EXPECT_EQ(cfg[1], 200);
+  lib::SVMDumper::DumpScaleFile(Node{5, "host-x", 14563}, TmpDir() + "scale");
+  Node n = lib::SVMDumper::LoadScaleFile(TmpDir() + "scale");
+  EXPECT_EQ(n.id, 5u);
+  EXPECT_EQ(n.port, 14563);
+}
+TEST(Io, BlockAssignerAndLineInputFormatDeliverEveryLineOnce) {
+  const std::string dir = TmpDir() + "data/";
+  io::MakeDirsFor(dir + "x");
+  const int rows = 997;
+  WriteLibsvm(dir + "part-0", rows);
+  WriteLibsvm(dir + "part-1", 10);
+  for (size_t block : {size_t(64), size_t(1000), size_t(1) << 20}) {
+    Node n0{0, "localhost", 0}, n1{1, "localhost", 0};
+    DataManager::Config cfg;
+    cfg.master_port = PortBase() + 18;
+    cfg.url = dir;
+    cfg.num_local_load_thread = 2;
+    cfg.block_size = block;
+    std::vector<SVMItem> store0, store1;
+    auto parse = [](const std::string& l, SVMItem* s) { return lib::Parser::parse_libsvm(l, s); };
+    std::thread other([&] { lib::DataLoader<SVMItem, std::vector<SVMItem>>::load(cfg, n1, {n0, n1}, parse, &store1); });
+    lib::DataLoader<SVMItem, std::vector<SVMItem>>::load(cfg, n0, {n0, n1}, parse, &store0);
+    other.join();
+    EXPECT_EQ(store0.size() + store1.size(), static_cast<size_t>(rows + 10));
+    size_t nnz = 0, expect = 0;
+    for (auto& s : store0) nnz += s.first.size();
+    for (auto& s : store1) nnz += s.first.size();
+    for (int r = 0; r < rows; ++r) expect += 1 + r % 5;
+    for (int r = 0; r < 10; ++r) expect += 1 + r % 5;
+    EXPECT_EQ(nnz, expect);
+  }
+}
+TEST(Io, AssignerPrefersLocalBlocks) {
+  const std::string f = TmpDir() + "blocks.txt";
+  { std::ofstream out(f); out << std::string(1000, 'x'); }
+  BlockAssigner a(PortBase() + 19, 0, 100);
+  auto first = a.Answer(f, "hostA");   // only hostA known: everything is "on" hostA
+  EXPECT_EQ(first.second, 0u);
+  int served = 1;
+  while (!a.Answer(f, "hostB").first.empty()) ++served;  // a remote host still gets work (dynamic balance)
+  EXPECT_EQ(served, 10);
+  EXPECT_TRUE(a.Answer(f, "hostA").first.empty());
+}
+TEST(Lib, AsyncDataLoaderPrefetchesBatches) {
+  const std::string f = TmpDir() + "async.libsvm";
+  WriteLibsvm(f, 103);
+  BlockAssigner assigner(PortBase() + 18, 1, 256);
+  assigner.StartAsync();
+  Coordinator coord(0, "localhost", "localhost", PortBase() + 18);
+  coord.serve();
+  LineInputFormat in(&coord, f, 1, 256);
+  lib::AsyncDataLoader<SVMItem> loader(&in, [](const std::string& l, SVMItem* s) { return lib::Parser::parse_libsvm(l, s); }, 10, 3);
+  size_t total = 0, batches = 0;
+  std::vector<SVMItem> batch;
+  while (loader.get_data(&batch)) {
+    total += batch.size();
+    ++batches;
+    EXPECT_TRUE(batch.size() <= 10);
+  }
+  EXPECT_EQ(total, 103u);
+  EXPECT_EQ(batches, 11u);
+  EXPECT_TRUE(loader.end_of_file());
+  BinStream bye;
+  coord.notify_master(bye, kAssignerExit);
+  assigner.Join();
+}
+
+int main(int argc, char** argv) {
+  const std::string filter = argc > 1 ? argv[1] : "";
+  if (filter == "--list") {
+    for (auto& t : Registry()) std::cout << t.name << "\n";
+    return 0;
+  }
+  int ran = 0, failed = 0;
+  for (auto& t : Registry()) {
+    if (!filter.empty() && t.name.find(filter) == std::string::npos) continue;
+    const int before = g_failures;
+    std::cout << "[ RUN  ] " << t.name << std::endl;
+    try {
+      t.fn();
+    } catch (const std::exception& e) {
+      ++g_failures;
+      std::cerr << "    uncaught: " << e.what() << "\n";
+    }
+    ++ran;
+    if (g_failures != before) {
+      ++failed;
+      std::cout << "[ FAIL ] " << t.name << std::endl;
+    } else {
+      std::cout << "[  OK  ] " << t.name << std::endl;
+    }
+  }
+  std::cout << ran << " tests, " << failed << " failed" << std::endl;
+  return failed ? 1 : 0;
+}
