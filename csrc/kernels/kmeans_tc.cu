@@ -1,0 +1,512 @@
+// kmeans_tc.cu — nearest-centre assignment on the 5th-gen tensor cores.
+//
+// Reference hot loop (apps/kmeans/kmeans_helper.hpp:45-66, called from apps/kmeans/kmeans.cpp:245):
+// for every point, for every one of the K centres, copy the D-vector, subtract the sparse
+// point and take the inner product — O(K*D) scalar work per point after a full-table pull of
+// the (K+1)*D centroid table (kmeans.cpp:223).  Here:
+//
+//   argmin_c ||x - c||^2  =  argmin_c ( ||c||^2 - 2 x.c )
+//
+// is one persistent, warp-specialised kernel:
+//   prologue  the centroid PULL fused into the B-operand fill: every CTA reads its slice of the
+//             fp32 centroid table straight from the owning shards (peer ld over NVLink),
+//             rounds to bf16 into the local B matrix and accumulates ||c||^2;
+//   warp 0    TMA producer: A tiles (128 points x D, bf16) and B chunks (128 centres x D) into
+//             128B-swizzled shared memory, mbarrier complete_tx;
+//   warp 1    issues tcgen05.mma (M=128, N=128, K=16, bf16 -> fp32) into a ring of four
+//             128-column TMEM accumulators; tcgen05.commit releases smem / signals the epilogue;
+//   warps 2-5 epilogue: tcgen05.ld the accumulator, d = ||c||^2 - 2 acc, running arg-min with
+//             the column index packed into the low mantissa bits (FFMA + LOP3 + FMNMX3 per
+//             element, no distance matrix ever touches memory).
+// A group of A_TILES point tiles stays resident in shared memory while the K/128 centre chunks
+// stream past it, so B is re-read from L2 only once per 128*A_TILES points.
+#include <cuda.h>
+#include <cuda_bf16.h>
+
+#include "common.cuh"
+
+namespace mps {
+namespace kmtc {
+
+constexpr int kTileM = 128;    // points per MMA tile
+constexpr int kChunkN = 128;   // centres per MMA chunk
+constexpr int kSlots = 4;      // TMEM accumulator ring (4 x 128 columns = all 512)
+constexpr int kBStages = 3;
+constexpr int kThreads = 192;  // warp 0 TMA, warp 1 MMA, warps 2..5 epilogue
+
+// ---------------------------------------------------------------- PTX wrappers
+__device__ __forceinline__ uint32_t smem_u32(const void* p) { return static_cast<uint32_t>(__cvta_generic_to_shared(p)); }
+
+__device__ __forceinline__ void mbar_init(uint64_t* bar, uint32_t count) {
+  asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count) : "memory");
+}
+__device__ __forceinline__ void mbar_expect_tx(uint64_t* bar, uint32_t bytes) {
+  asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void mbar_arrive(uint64_t* bar) {
+  asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smem_u32(bar)) : "memory");
+}
+__device__ __forceinline__ bool mbar_try_wait(uint64_t* bar, uint32_t parity) {
+  uint32_t ok;
+  asm volatile(
+      "{\n"
+      ".reg .pred P1;\n"
+      "mbarrier.try_wait.parity.shared::cta.b64 P1, [%1], %2;\n"
+      "selp.u32 %0, 1, 0, P1;\n"
+      "}\n"
+      : "=r"(ok)
+      : "r"(smem_u32(bar)), "r"(parity)
+      : "memory");
+  return ok != 0;
+}
+// try_wait suspends in hardware for a bounded time; the loop re-arms it.  A (generous) clock
+// budget turns a protocol bug into a trap with an error code instead of a hung GPU.
+__device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
+  if (mbar_try_wait(bar, parity)) return;
+  const long long t0 = clock64();
+  while (!mbar_try_wait(bar, parity)) {
+    if (clock64() - t0 > 20000000000LL) __trap();
+  }
+}
+__device__ __forceinline__ void fence_barrier_init() { asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory"); }
+__device__ __forceinline__ void fence_proxy_async() { asm volatile("fence.proxy.async;" ::: "memory"); }
+__device__ __forceinline__ bool elect_one() {
+  uint32_t pred;
+  asm volatile(
+      "{\n"
+      ".reg .pred P;\n"
+      "elect.sync _|P, 0xffffffff;\n"
+      "selp.u32 %0, 1, 0, P;\n"
+      "}\n"
+      : "=r"(pred));
+  return pred != 0;
+}
+__device__ __forceinline__ void tma_load_2d(void* smem_dst, const CUtensorMap* map, uint64_t* bar, int c0, int c1) {
+  asm volatile(
+      "cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4}], [%2];" ::"r"(
+          smem_u32(smem_dst)),
+      "l"(map), "r"(smem_u32(bar)), "r"(c0), "r"(c1)
+      : "memory");
+}
+__device__ __forceinline__ void tmem_alloc(uint32_t* smem_dst, uint32_t cols) {
+  asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(smem_dst)), "r"(cols)
+               : "memory");
+  asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+}
+__device__ __forceinline__ void tmem_dealloc(uint32_t taddr, uint32_t cols) {
+  asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(taddr), "r"(cols) : "memory");
+}
+__device__ __forceinline__ void tc_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
+__device__ __forceinline__ void tc_fence_after() { asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory"); }
+__device__ __forceinline__ void umma_bf16(uint32_t d_tmem, uint64_t a_desc, uint64_t b_desc, uint32_t idesc, uint32_t acc) {
+  asm volatile(
+      "{\n"
+      ".reg .pred p;\n"
+      "setp.ne.b32 p, %4, 0;\n"
+      "tcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n"
+      "}\n" ::"r"(d_tmem),
+      "l"(a_desc), "l"(b_desc), "r"(idesc), "r"(acc)
+      : "memory");
+}
+__device__ __forceinline__ void umma_commit(uint64_t* bar) {
+  asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(smem_u32(bar))
+               : "memory");
+}
+__device__ __forceinline__ void tmem_ld32(uint32_t taddr, uint32_t (&r)[32]) {
+  asm volatile(
+      "tcgen05.ld.sync.aligned.32x32b.x32.b32 "
+      "{%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, "
+      "%16, %17, %18, %19, %20, %21, %22, %23, %24, %25, %26, %27, %28, %29, %30, %31}, [%32];"
+      : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]), "=r"(r[8]),
+        "=r"(r[9]), "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15]), "=r"(r[16]),
+        "=r"(r[17]), "=r"(r[18]), "=r"(r[19]), "=r"(r[20]), "=r"(r[21]), "=r"(r[22]), "=r"(r[23]), "=r"(r[24]),
+        "=r"(r[25]), "=r"(r[26]), "=r"(r[27]), "=r"(r[28]), "=r"(r[29]), "=r"(r[30]), "=r"(r[31])
+      : "r"(taddr)
+      : "memory");
+}
+__device__ __forceinline__ void tmem_ld_wait() { asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory"); }
+__device__ __forceinline__ float fmin3(float a, float b, float c) {
+  float d;
+  asm("min.f32 %0, %1, %2, %3;" : "=f"(d) : "f"(a), "f"(b), "f"(c));
+  return d;
+}
+
+// K-major, 128B-swizzled operand block [rows x 64 bf16]: 8-row groups are 1024 B apart (SBO),
+// descriptor version 1 (sm_100), layout type 2 = SWIZZLE_128B.  Advancing K by 16 elements
+// inside the 128-byte swizzle atom = +32 bytes on the start address.
+__device__ __forceinline__ uint64_t umma_smem_desc(uint32_t smem_addr) {
+  uint64_t d = 0;
+  d |= static_cast<uint64_t>((smem_addr & 0x3FFFF) >> 4);  // start address, bits [0,14)
+  d |= static_cast<uint64_t>(1) << 16;                     // LBO (unused for swizzled K-major)
+  d |= static_cast<uint64_t>(1024 >> 4) << 32;             // SBO = 1024 B
+  d |= static_cast<uint64_t>(1) << 46;                     // descriptor version (Blackwell)
+  d |= static_cast<uint64_t>(2) << 61;                     // SWIZZLE_128B
+  return d;
+}
+// kind::f16 instruction descriptor: D = F32, A = B = BF16, both K-major, M x N
+__host__ __device__ constexpr uint32_t umma_idesc(int M, int N) {
+  return (1u << 4) | (1u << 7) | (1u << 10) | (static_cast<uint32_t>(N >> 3) << 17) |
+         (static_cast<uint32_t>(M >> 4) << 24);
+}
+
+struct Params {
+  MpsTableView centers;          // fp32 centroid table (K*D keys, range-partitioned)
+  int has_view;                  // 0: centres_f32 below is a local dense [K, D] array instead
+  const float* centers_f32;
+  __nv_bfloat16* centers_bf16;   // [K, D] scratch: the bf16 B operand (TMA source)
+  float* cnorm;                  // [K] scratch: ||c||^2 of the rounded centres
+  int* sync_ctr;                 // zeroed grid-barrier counter
+  int32_t* assign;               // [n] out
+  float* dist;                   // [n] out: ||c||^2 - 2 x.c of the chosen centre (add ||x||^2 for the SSE)
+  int64_t n;
+  int K;
+  MpsClockView clk;              // consistency gate of the centroid table (gated != 0)
+  int gated;
+  int progress;
+  float* centers_f32_out;        // optional [K, D]: fp32 copy of the pulled centres (for the update step)
+};
+
+template <int kAtoms>  // D = 64 * kAtoms
+struct Smem {
+  static constexpr int D = 64 * kAtoms;
+  static constexpr int kATiles = (D <= 128) ? 3 : 1;
+  static constexpr int kTileBytes = kTileM * D * 2;
+  static constexpr int kChunkBytes = kChunkN * D * 2;
+  static constexpr int kABytes = kATiles * kTileBytes;
+  static constexpr int kBBytes = kBStages * kChunkBytes;
+  static constexpr int kBarOff = kABytes + kBBytes;
+  static constexpr int kNumBars = 2 * kATiles + 2 * kBStages + 2 * kSlots;
+  static constexpr int kCnormOff = kBarOff + 8 * kNumBars + 16;
+  static int bytes(int K) { return kCnormOff + K * 4 + 1024; }
+};
+
+template <int kAtoms>
+__global__ void __launch_bounds__(kThreads, 1)
+kmeans_assign_tc_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_constant__ CUtensorMap map_c,
+                        const __grid_constant__ Params p) {
+  using S = Smem<kAtoms>;
+  constexpr int D = S::D;
+  constexpr int kATiles = S::kATiles;
+  constexpr int kKSteps = D / 16;
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  uint8_t* sA = smem;
+  uint8_t* sB = smem + S::kABytes;
+  uint64_t* bars = reinterpret_cast<uint64_t*>(smem + S::kBarOff);
+  uint64_t* a_full = bars;
+  uint64_t* a_empty = a_full + kATiles;
+  uint64_t* b_full = a_empty + kATiles;
+  uint64_t* b_empty = b_full + kBStages;
+  uint64_t* t_full = b_empty + kBStages;
+  uint64_t* t_empty = t_full + kSlots;
+  uint32_t* tmem_base_smem = reinterpret_cast<uint32_t*>(t_empty + kSlots);
+  float* s_cnorm = reinterpret_cast<float*>(smem + S::kCnormOff);
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int K = p.K;
+  const int n_chunks = K / kChunkN;
+
+  // ---------------------------------------------------------- prologue: pull + round + norms
+  if (p.gated) cta_gate(p.clk, p.progress);
+  {
+    const int64_t gwarp = (static_cast<int64_t>(blockIdx.x) * kThreads + threadIdx.x) >> 5;
+    const int64_t nwarps = (static_cast<int64_t>(gridDim.x) * kThreads) >> 5;
+    for (int64_t c = gwarp; c < K; c += nwarps) {
+      float sq = 0.f;
+      for (int d0 = lane * 4; d0 < D; d0 += 128) {
+        float4 v;
+        const int64_t flat = c * D + d0;
+        if (p.has_view) {
+          const uint32_t key = p.centers.begin[0] + static_cast<uint32_t>(flat);
+          const int s = owner_of(p.centers, key);
+          const float* src = static_cast<const float*>(p.centers.weights[s]) + (key - p.centers.begin[s]);
+          // shard boundaries fall on multiples of 4 keys whenever D % 4 == 0 and ranges are row aligned
+          if (key + 3 < p.centers.begin[s + 1] && ((key - p.centers.begin[s]) & 3) == 0) {
+            v = ld_sys_v4(src);
+          } else {
+            float t[4];
+            for (int j = 0; j < 4; ++j) {
+              const uint32_t kj = key + j;
+              const int sj = owner_of(p.centers, kj);
+              t[j] = ld_sys(static_cast<const float*>(p.centers.weights[sj]) + (kj - p.centers.begin[sj]));
+            }
+            v = make_float4(t[0], t[1], t[2], t[3]);
+          }
+        } else {
+          v = *reinterpret_cast<const float4*>(p.centers_f32 + flat);
+        }
+        __nv_bfloat162 lo = __floats2bfloat162_rn(v.x, v.y), hi = __floats2bfloat162_rn(v.z, v.w);
+        uint2 packed;
+        packed.x = *reinterpret_cast<uint32_t*>(&lo);
+        packed.y = *reinterpret_cast<uint32_t*>(&hi);
+        *reinterpret_cast<uint2*>(p.centers_bf16 + flat) = packed;
+        if (p.centers_f32_out) *reinterpret_cast<float4*>(p.centers_f32_out + flat) = v;
+        const float2 flo = __bfloat1622float2(lo), fhi = __bfloat1622float2(hi);
+        sq += flo.x * flo.x + flo.y * flo.y + fhi.x * fhi.x + fhi.y * fhi.y;
+      }
+      sq = warp_sum(sq);
+      if (lane == 0) p.cnorm[c] = sq;
+    }
+    // the B matrix is consumed by TMA (async proxy): order the generic-proxy writes before it
+    fence_proxy_async();
+    GridBarrier gb{p.sync_ctr, 0};
+    gb.sync();
+  }
+  for (int i = threadIdx.x; i < K; i += kThreads) s_cnorm[i] = ld_cg(p.cnorm + i);
+
+  // ---------------------------------------------------------- barriers + TMEM
+  if (threadIdx.x == 0) {
+    for (int i = 0; i < kATiles; ++i) { mbar_init(a_full + i, 1); mbar_init(a_empty + i, 1); }
+    for (int i = 0; i < kBStages; ++i) { mbar_init(b_full + i, 1); mbar_init(b_empty + i, 1); }
+    for (int i = 0; i < kSlots; ++i) { mbar_init(t_full + i, 1); mbar_init(t_empty + i, 4); }
+    fence_barrier_init();
+  }
+  if (warp == 1) tmem_alloc(tmem_base_smem, 512);
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_base_smem;
+
+  const int64_t group_rows = static_cast<int64_t>(kATiles) * kTileM;
+  const int64_t n_groups = (p.n + group_rows - 1) / group_rows;
+
+  if (warp == 0) {
+    // ======================================================= TMA producer
+    if (elect_one()) {
+      uint32_t gi = 0, bi = 0;
+      for (int64_t g = blockIdx.x; g < n_groups; g += gridDim.x, ++gi) {
+        for (int c = 0; c < n_chunks; ++c, ++bi) {
+          const uint32_t st = bi % kBStages;
+          mbar_wait(b_empty + st, ((bi / kBStages) & 1) ^ 1);
+          mbar_expect_tx(b_full + st, S::kChunkBytes);
+          for (int a = 0; a < kAtoms; ++a)
+            tma_load_2d(sB + st * S::kChunkBytes + a * (kChunkN * 128), &map_c, b_full + st, a * 64, c * kChunkN);
+          if (c == 0) {
+            for (int t = 0; t < kATiles; ++t) {
+              mbar_wait(a_empty + t, (gi & 1) ^ 1);
+              mbar_expect_tx(a_full + t, S::kTileBytes);
+              const int row0 = static_cast<int>(g * group_rows + t * kTileM);
+              for (int a = 0; a < kAtoms; ++a)
+                tma_load_2d(sA + t * S::kTileBytes + a * (kTileM * 128), &map_x, a_full + t, a * 64, row0);
+            }
+          }
+        }
+      }
+    }
+  } else if (warp == 1) {
+    // ======================================================= MMA issuer
+    constexpr uint32_t idesc = umma_idesc(kTileM, kChunkN);
+    uint32_t gi = 0, bi = 0, ui = 0;
+    for (int64_t g = blockIdx.x; g < n_groups; g += gridDim.x, ++gi) {
+      for (int c = 0; c < n_chunks; ++c, ++bi) {
+        const uint32_t st = bi % kBStages;
+        mbar_wait(b_full + st, (bi / kBStages) & 1);
+        for (int t = 0; t < kATiles; ++t, ++ui) {
+          if (c == 0) mbar_wait(a_full + t, gi & 1);
+          const uint32_t slot = ui % kSlots;
+          mbar_wait(t_empty + slot, ((ui / kSlots) & 1) ^ 1);
+          tc_fence_after();
+          if (elect_one()) {
+            const uint32_t d_tmem = tmem_base + slot * kChunkN;
+#pragma unroll
+            for (int k = 0; k < kKSteps; ++k) {
+              const int atom = k / 4, sub = k % 4;
+              const uint64_t da = umma_smem_desc(smem_u32(sA + t * S::kTileBytes + atom * (kTileM * 128)) + sub * 32);
+              const uint64_t db = umma_smem_desc(smem_u32(sB + st * S::kChunkBytes + atom * (kChunkN * 128)) + sub * 32);
+              umma_bf16(d_tmem, da, db, idesc, k > 0 ? 1u : 0u);
+            }
+            umma_commit(t_full + slot);
+            if (t == kATiles - 1) umma_commit(b_empty + st);
+            if (c == n_chunks - 1) umma_commit(a_empty + t);
+          }
+          __syncwarp();
+        }
+      }
+    }
+  } else {
+    // ======================================================= epilogue (warps 2..5)
+    const int quarter = warp & 3;  // TMEM lanes [32*quarter, 32*quarter + 32)
+    uint32_t ui = 0;
+    for (int64_t g = blockIdx.x; g < n_groups; g += gridDim.x) {
+      float best[kATiles];
+      int bestc[kATiles];
+#pragma unroll
+      for (int t = 0; t < kATiles; ++t) { best[t] = __int_as_float(0x7f7fffff); bestc[t] = 0; }
+      for (int c = 0; c < n_chunks; ++c) {
+#pragma unroll
+        for (int t = 0; t < kATiles; ++t, ++ui) {
+          const uint32_t slot = ui % kSlots;
+          mbar_wait(t_full + slot, (ui / kSlots) & 1);
+          tc_fence_after();
+          float m = __int_as_float(0x7f7fffff);
+#pragma unroll
+          for (int sub = 0; sub < 4; ++sub) {
+            uint32_t r[32];
+            tmem_ld32(tmem_base + (static_cast<uint32_t>(quarter * 32) << 16) + slot * kChunkN + sub * 32, r);
+            tmem_ld_wait();
+            const float4* cn4 = reinterpret_cast<const float4*>(s_cnorm + c * kChunkN + sub * 32);
+#pragma unroll
+            for (int j = 0; j < 32; j += 4) {
+              const float4 cn = cn4[j >> 2];
+              const float d0 = fmaf(__uint_as_float(r[j + 0]), -2.f, cn.x);
+              const float d1 = fmaf(__uint_as_float(r[j + 1]), -2.f, cn.y);
+              const float d2 = fmaf(__uint_as_float(r[j + 2]), -2.f, cn.z);
+              const float d3 = fmaf(__uint_as_float(r[j + 3]), -2.f, cn.w);
+              const float q0 = __uint_as_float((__float_as_uint(d0) & 0xFFFFFF80u) | static_cast<uint32_t>(sub * 32 + j + 0));
+              const float q1 = __uint_as_float((__float_as_uint(d1) & 0xFFFFFF80u) | static_cast<uint32_t>(sub * 32 + j + 1));
+              const float q2 = __uint_as_float((__float_as_uint(d2) & 0xFFFFFF80u) | static_cast<uint32_t>(sub * 32 + j + 2));
+              const float q3 = __uint_as_float((__float_as_uint(d3) & 0xFFFFFF80u) | static_cast<uint32_t>(sub * 32 + j + 3));
+              m = fmin3(m, q0, q1);
+              m = fmin3(m, q2, q3);
+            }
+          }
+          // accumulator drained: hand the slot back to the MMA warp
+          tc_fence_before();
+          __syncwarp();
+          if (lane == 0) mbar_arrive(t_empty + slot);
+          if (m < best[t]) { best[t] = m; bestc[t] = c; }
+        }
+      }
+#pragma unroll
+      for (int t = 0; t < kATiles; ++t) {
+        const int64_t row = g * group_rows + t * kTileM + quarter * 32 + lane;
+        if (row < p.n) {
+          const uint32_t bits = __float_as_uint(best[t]);
+          p.assign[row] = bestc[t] * kChunkN + static_cast<int>(bits & 127u);
+          p.dist[row] = __uint_as_float(bits & 0xFFFFFF80u);
+        }
+      }
+    }
+  }
+
+  // ---------------------------------------------------------- teardown
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 1) tmem_dealloc(tmem_base, 512);
+}
+
+// Plain CUDA-core kernel of the same operation on the same bf16-rounded inputs: the
+// differential reference for tests and the "recompiled legacy path" timing baseline.
+__global__ void __launch_bounds__(256)
+kmeans_assign_ref_kernel(const __nv_bfloat16* __restrict__ x, const __nv_bfloat16* __restrict__ c,
+                         const float* __restrict__ cnorm, int64_t n, int K, int D, int32_t* __restrict__ assign,
+                         float* __restrict__ dist) {
+  const int64_t row = static_cast<int64_t>(blockIdx.x) * blockDim.x + threadIdx.x;
+  if (row >= n) return;
+  float best = 3.4e38f;
+  int bi = 0;
+  for (int k = 0; k < K; ++k) {
+    float acc = 0.f;
+    for (int d = 0; d < D; ++d) acc = fmaf(__bfloat162float(x[row * D + d]), __bfloat162float(c[static_cast<int64_t>(k) * D + d]), acc);
+    const float v = fmaf(acc, -2.f, cnorm[k]);
+    if (v < best) { best = v; bi = k; }
+  }
+  assign[row] = bi;
+  dist[row] = best;
+}
+
+typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
+                                  const cuuint64_t*, const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave,
+                                  CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+
+static EncodeTiledFn get_encode() {
+  static EncodeTiledFn fn = nullptr;
+  if (!fn) {
+    void* ptr = nullptr;
+    cudaDriverEntryPointQueryResult q;
+    if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &ptr, cudaEnableDefault, &q) == cudaSuccess &&
+        q == cudaDriverEntryPointSuccess)
+      fn = reinterpret_cast<EncodeTiledFn>(ptr);
+  }
+  return fn;
+}
+
+// 2-D bf16 row-major [rows, D] tensor, box = 64 columns (128 B) x 128 rows, 128B swizzle
+static int make_map(CUtensorMap* map, const void* base, int64_t rows, int D) {
+  EncodeTiledFn enc = get_encode();
+  if (!enc) return static_cast<int>(cudaErrorNotSupported);
+  cuuint64_t dims[2] = {static_cast<cuuint64_t>(D), static_cast<cuuint64_t>(rows)};
+  cuuint64_t strides[1] = {static_cast<cuuint64_t>(D) * 2};
+  cuuint32_t box[2] = {64, 128};
+  cuuint32_t estr[2] = {1, 1};
+  CUresult r = enc(map, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, const_cast<void*>(base), dims, strides, box, estr,
+                   CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                   CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  return r == CUDA_SUCCESS ? 0 : static_cast<int>(cudaErrorInvalidValue);
+}
+
+template <int kAtoms>
+static int launch(const Params& p, const void* x, int max_ctas, cudaStream_t st) {
+  using S = Smem<kAtoms>;
+  CUtensorMap map_x, map_c;
+  int rc = make_map(&map_x, x, p.n, S::D);
+  if (rc) return rc;
+  rc = make_map(&map_c, p.centers_bf16, p.K, S::D);
+  if (rc) return rc;
+  const int smem = S::bytes(p.K);
+  auto kern = kmeans_assign_tc_kernel<kAtoms>;
+  MPS_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+  int dev = 0, sms = 148;
+  cudaGetDevice(&dev);
+  cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+  const int64_t group_rows = static_cast<int64_t>(S::kATiles) * kTileM;
+  const int64_t n_groups = (p.n + group_rows - 1) / group_rows;
+  int grid = static_cast<int>(n_groups < sms ? n_groups : sms);
+  if (max_ctas > 0 && grid > max_ctas) grid = max_ctas;
+  if (grid < 1) grid = 1;
+  MPS_CHECK(cudaMemsetAsync(p.sync_ctr, 0, sizeof(int), st));
+  Params pp = p;
+  void* args[] = {&map_x, &map_c, &pp};
+  MPS_CHECK(cudaLaunchCooperativeKernel(reinterpret_cast<void*>(kern), dim3(grid), dim3(kThreads), args, smem, st));
+  return 0;
+}
+
+}  // namespace kmtc
+}  // namespace mps
+
+extern "C" {
+
+int mps_kmeans_assign_tc(const MpsTableView* centers_view, const MpsClockView* clk, int progress,
+                         const float* centers_f32, const void* x_bf16, int64_t n, int K, int D,
+                         void* centers_bf16_scratch, float* cnorm_scratch, float* centers_f32_out, int* sync_ctr,
+                         int32_t* assign, float* dist, int max_ctas, void* stream) {
+  if (n <= 0) return 0;
+  if (K % mps::kmtc::kChunkN != 0 || K <= 0 || K > 8192) return static_cast<int>(cudaErrorInvalidValue);
+  mps::kmtc::Params p{};
+  if (centers_view) {
+    p.centers = *centers_view;
+    p.has_view = 1;
+    if (centers_view->dtype != MPS_F32) return static_cast<int>(cudaErrorInvalidValue);
+  } else {
+    p.has_view = 0;
+  }
+  p.centers_f32 = centers_f32;
+  p.centers_bf16 = static_cast<__nv_bfloat16*>(centers_bf16_scratch);
+  p.cnorm = cnorm_scratch;
+  p.sync_ctr = sync_ctr;
+  p.assign = assign;
+  p.dist = dist;
+  p.n = n;
+  p.K = K;
+  p.gated = (clk != nullptr && centers_view != nullptr) ? 1 : 0;
+  if (p.gated) p.clk = *clk;
+  p.progress = progress;
+  p.centers_f32_out = centers_f32_out;
+  auto st = static_cast<cudaStream_t>(stream);
+  if (D == 64) return mps::kmtc::launch<1>(p, x_bf16, max_ctas, st);
+  if (D == 128) return mps::kmtc::launch<2>(p, x_bf16, max_ctas, st);
+  return static_cast<int>(cudaErrorInvalidValue);
+}
+
+int mps_kmeans_assign_ref(const void* x_bf16, const void* centers_bf16, const float* cnorm, int64_t n, int K, int D,
+                          int32_t* assign, float* dist, void* stream) {
+  if (n <= 0) return 0;
+  const int grid = static_cast<int>((n + 255) / 256);
+  mps::kmtc::kmeans_assign_ref_kernel<<<grid, 256, 0, static_cast<cudaStream_t>(stream)>>>(
+      static_cast<const __nv_bfloat16*>(x_bf16), static_cast<const __nv_bfloat16*>(centers_bf16), cnorm, n, K, D,
+      assign, dist);
+  MPS_LAUNCH_CHECK();
+  return 0;
+}
+
+}  // extern "C"

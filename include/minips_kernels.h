@@ -187,6 +187,32 @@ int mps_lr_train_dense_noalloc(const MpsTableView* view, const MpsClockView* clk
 int mps_lr_eval(const float* weights, const MpsCsr* csr, int64_t row_begin, int64_t n,
                 float* out, void* stream);
 
+/* ---- mini-batch k-means (csrc/kernels/kmeans_tc.cu, kmeans.cu) ----------------------- */
+/* Nearest-centre assignment (apps/kmeans/kmeans_helper.hpp:45-66) as a tcgen05/TMEM/TMA GEMM
+ * with the arg-min fused into the TMEM epilogue and the centroid pull (kmeans.cpp:223) fused
+ * into the B-operand fill.  x_bf16: [n, D] row-major bf16 points (D = 64 or 128); centres come
+ * either from a range-partitioned fp32 table view of K*D keys (row-major, peer loads, optional
+ * consistency gate clk/progress) or, when centers_view is NULL, from the local dense array
+ * centers_f32.  K must be a multiple of 128.  Scratch: centers_bf16_scratch [K*D] bf16,
+ * cnorm_scratch [K] f32, sync_ctr [1] int.  Outputs: assign [n] int32, dist [n] f32 =
+ * ||c||^2 - 2 x.c of the chosen centre (add ||x||^2 for the squared distance); optional
+ * centers_f32_out [K*D] receives the pulled fp32 centres. */
+int mps_kmeans_assign_tc(const MpsTableView* centers_view, const MpsClockView* clk, int progress,
+                         const float* centers_f32, const void* x_bf16, int64_t n, int K, int D,
+                         void* centers_bf16_scratch, float* cnorm_scratch, float* centers_f32_out,
+                         int* sync_ctr, int32_t* assign, float* dist, int max_ctas, void* stream);
+/* CUDA-core kernel of the same operation on the same bf16 inputs (differential reference). */
+int mps_kmeans_assign_ref(const void* x_bf16, const void* centers_bf16, const float* cnorm, int64_t n,
+                          int K, int D, int32_t* assign, float* dist, void* stream);
+/* Per-cluster partial sums / counts of a batch (kmeans.cpp:247-263 in batched form) and its SSE
+ * (kmeans_helper.hpp:236-266): sums [K*D] += x, counts [K] += 1, sse[0] += ||x - c||^2. */
+int mps_kmeans_accumulate(const void* x_bf16, const int32_t* assign, const float* dist, int64_t n,
+                          int K, int D, float* sums, float* counts, float* sse, void* stream);
+/* Centroid normalisation: delta_c = alpha (sum - m c) / (n_old + m), delta_n = m. */
+int mps_kmeans_delta(const float* centers, const float* counts_old, const float* sums,
+                     const float* counts_batch, int K, int D, float alpha, float* delta_c,
+                     float* delta_n, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -123,6 +123,11 @@ def _declare(lib):
         "mps_lr_train_dense_ex": ([P(TableView), P(ClockView), i32, i32, P(Csr), vp, i32, i64, f32, vp, vp, vp,
                                    vp, i32, i32, vp], i32),
         "mps_lr_eval": ([vp, P(Csr), i64, i64, vp, vp], i32),
+        "mps_kmeans_assign_tc": ([P(TableView), P(ClockView), i32, vp, vp, i64, i32, i32, vp, vp, vp, vp, vp, vp,
+                                  i32, vp], i32),
+        "mps_kmeans_assign_ref": ([vp, vp, vp, i64, i32, i32, vp, vp, vp], i32),
+        "mps_kmeans_accumulate": ([vp, vp, vp, i64, i32, i32, vp, vp, vp, vp], i32),
+        "mps_kmeans_delta": ([vp, vp, vp, vp, i32, i32, f32, vp, vp, vp], i32),
     }
     for name, (argtypes, restype) in sig.items():
         if hasattr(lib, name):
