@@ -39,7 +39,8 @@ class KMeansAssigner:
         assert K % 128 == 0 and D in (64, 128), "tcgen05 path: K multiple of 128, D in {64, 128}"
         self.K, self.D, self.dev = K, D, device
         self.lib = _lib.load()
-        self.c_bf16 = torch.empty(K * D, dtype=torch.bfloat16, device=device)
+        # B-operand scratch: [K, D] bf16(-2c) | [K, 64] ||c||^2 as a 3-way bf16 split | [128, 64] ones
+        self.c_bf16 = torch.empty(K * D + K * 64 + 128 * 64, dtype=torch.bfloat16, device=device)
         self.cnorm = torch.empty(K, dtype=torch.float32, device=device)
         self.c_f32 = torch.empty(K * D, dtype=torch.float32, device=device)
         self.sync = torch.zeros(4, dtype=torch.int32, device=device)

@@ -37,9 +37,13 @@ def test_assign_tc_matches_oracle(n, K, D):
     _, _, d_full = oracle_assign(x, centers)
     _check_objective(assign, dist, d_full)
     # the fused prologue left the rounded centres, their norms and the fp32 copy behind
-    torch.testing.assert_close(km.c_bf16.view(K, D), centers.to(torch.bfloat16))
+    torch.testing.assert_close(km.c_bf16[:K * D].view(K, D).float(), -2.0 * centers.to(torch.bfloat16).float())
     cf = centers.to(torch.bfloat16).float()
     torch.testing.assert_close(km.cnorm, (cf * cf).sum(1), rtol=1e-5, atol=1e-4)
+    # ||c||^2 rides into the accumulator as hi + mid + lo (bf16) through one extra MMA step
+    aug = km.c_bf16[K * D:K * D + K * 64].view(K, 64).float()
+    torch.testing.assert_close(aug[:, :3].sum(1), km.cnorm, rtol=1e-6, atol=1e-5)
+    assert float(aug[:, 3:].abs().sum()) == 0.0
     torch.testing.assert_close(km.c_f32.view(K, D), centers)
     # differential: plain CUDA-core kernel on the same rounded inputs
     a_ref, d_ref = km.assign_ref(x[:2048])
