@@ -187,6 +187,49 @@ int mps_lr_train_dense_noalloc(const MpsTableView* view, const MpsClockView* clk
 int mps_lr_eval(const float* weights, const MpsCsr* csr, int64_t row_begin, int64_t n,
                 float* out, void* stream);
 
+/* ---- sparse helpers (csrc/kernels/sparse_utils.cu) ----------------------------------- */
+/* Sorted unique feature ids of a batch (lib/batch_data_sampler.cpp:50-71) and, optionally,
+ * the slot of every non-zero in that key list.  scratch_u32: 2*ceil(num_dims/32) +
+ * ceil(ceil(num_dims/32)/4096) + 2 words.  keys_out ascending; count_out[0] = #keys.
+ * slots_out[j - nnz_base] for the batch's non-zeros j (non-wrapping batches). */
+int mps_batch_unique_keys(const MpsCsr* csr, int64_t row_begin, int64_t batch, uint32_t num_dims,
+                          uint32_t* scratch_u32, uint32_t* keys_out, uint32_t* count_out,
+                          int32_t* slots_out, int64_t nnz_base, void* stream);
+/* libsvm text -> CSR on device (lib/parser.hpp:17-47, io/line_input_format.hpp:43-121), three
+ * passes so the caller can size the outputs between them:
+ *  1 scan_lines : line_end[k] = offset of the k-th line terminator, counts_out[0] = #lines
+ *                 (scratch_u32: ceil((nbytes+1)/4096)+2 words)
+ *  2 index_lines: valid/nnz per line, row_of_line, nnz_prefix, row_ptr[row];
+ *                 counts_out[1] = #rows, counts_out[2] = #nnz
+ *  3 parse      : col (0-based, file is 1-based), val, label (optionally y<0 -> 0) */
+int mps_libsvm_scan_lines(const char* text, int64_t nbytes, int64_t* line_end, uint32_t* scratch_u32,
+                          uint32_t* counts_out, void* stream);
+int mps_libsvm_index_lines(const char* text, const int64_t* line_end, int64_t n_lines, uint32_t* valid,
+                           uint32_t* nnz, int64_t* row_of_line, int64_t* nnz_prefix, int64_t* row_ptr,
+                           uint32_t* scratch_u32, uint32_t* counts_out, void* stream);
+int mps_libsvm_parse(const char* text, const int64_t* line_end, int64_t n_lines,
+                     const int64_t* row_of_line, const int64_t* nnz_prefix, uint32_t* col, float* val,
+                     float* label, int map_negative_label_to_zero, void* stream);
+
+/* ---- MapStorage on device (csrc/kernels/hash_table.cu) -------------------------------- */
+/* Range-partitioned open-addressing hash shards (server/map_storage.hpp:13-26): keys[s] /
+ * vals[s] address shard s's [capacity[s]] u32 keys (0xFFFFFFFF = empty) and f32 values, local
+ * or peer-mapped; capacity is a power of two. */
+typedef struct MpsHashView {
+  void* keys[MPS_MAX_SHARDS];
+  void* vals[MPS_MAX_SHARDS];
+  uint32_t capacity[MPS_MAX_SHARDS];
+  uint32_t begin[MPS_MAX_SHARDS + 1];
+  int32_t num_shards;
+} MpsHashView;
+int mps_hash_clear(void* keys, void* vals, int64_t capacity, void* stream);
+int mps_hash_add(const MpsHashView* view, const uint32_t* keys, const float* vals, int64_t n,
+                 int* overflow_flag, void* stream);
+int mps_hash_get(const MpsHashView* view, const MpsClockView* clk, int progress, const uint32_t* keys,
+                 float* vals, int64_t n, void* stream);
+int mps_hash_export(const void* keys, const void* vals, int64_t capacity, uint32_t* out_keys,
+                    float* out_vals, int* count, void* stream);
+
 /* ---- mini-batch k-means (csrc/kernels/kmeans_tc.cu, kmeans.cu) ----------------------- */
 /* Nearest-centre assignment (apps/kmeans/kmeans_helper.hpp:45-66) as a tcgen05/TMEM/TMA GEMM
  * with the arg-min fused into the TMEM epilogue and the centroid pull (kmeans.cpp:223) fused

@@ -63,6 +63,16 @@ class Csr(C.Structure):
     ]
 
 
+class HashView(C.Structure):
+    _fields_ = [
+        ("keys", C.c_void_p * MAX_SHARDS),
+        ("vals", C.c_void_p * MAX_SHARDS),
+        ("capacity", C.c_uint32 * MAX_SHARDS),
+        ("begin", C.c_uint32 * (MAX_SHARDS + 1)),
+        ("num_shards", C.c_int32),
+    ]
+
+
 _LIB_PATH = Path(__file__).resolve().parent.parent / "lib" / "libminips_kernels.so"
 _lib = None
 
@@ -123,6 +133,14 @@ def _declare(lib):
         "mps_lr_train_dense_ex": ([P(TableView), P(ClockView), i32, i32, P(Csr), vp, i32, i64, f32, vp, vp, vp,
                                    vp, i32, i32, vp], i32),
         "mps_lr_eval": ([vp, P(Csr), i64, i64, vp, vp], i32),
+        "mps_batch_unique_keys": ([P(Csr), i64, i64, C.c_uint32, vp, vp, vp, vp, i64, vp], i32),
+        "mps_libsvm_scan_lines": ([vp, i64, vp, vp, vp, vp], i32),
+        "mps_libsvm_index_lines": ([vp, vp, i64, vp, vp, vp, vp, vp, vp, vp, vp], i32),
+        "mps_libsvm_parse": ([vp, vp, i64, vp, vp, vp, vp, vp, i32, vp], i32),
+        "mps_hash_clear": ([vp, vp, i64, vp], i32),
+        "mps_hash_add": ([P(HashView), vp, vp, i64, vp, vp], i32),
+        "mps_hash_get": ([P(HashView), P(ClockView), i32, vp, vp, i64, vp], i32),
+        "mps_hash_export": ([vp, vp, i64, vp, vp, vp, vp], i32),
         "mps_kmeans_assign_tc": ([P(TableView), P(ClockView), i32, vp, vp, i64, i32, i32, vp, vp, vp, vp, vp, vp,
                                   i32, vp], i32),
         "mps_kmeans_assign_ref": ([vp, vp, vp, i64, i32, i32, vp, vp, vp], i32),

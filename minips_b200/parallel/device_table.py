@@ -45,7 +45,7 @@ class DeviceTable:
     def __init__(self, table_id: int, ranges: Sequence[Range], shard_owner: Sequence[int],
                  control: _ControlPlane, model_type: ModelType = ModelType.SSP, staleness: int = 0,
                  storage_type: StorageType = StorageType.Vector, dtype: torch.dtype = torch.float32,
-                 vals_per_key: int = 1, device: Optional[int] = None):
+                 vals_per_key: int = 1, device: Optional[int] = None, hash_capacity: Optional[int] = None):
         assert len(ranges) == len(shard_owner) and 0 < len(ranges) <= _lib.MAX_SHARDS
         assert dtype in (torch.float32, torch.float64)
         self.lib = _lib.load()
@@ -74,9 +74,19 @@ class DeviceTable:
         self.soff: List[int] = [0] * self.num_shards
         per_rank = [0] * self.world
         bsp = self.model_type == ModelType.BSP
+        # MapStorage on device (server/map_storage.hpp): every shard is an open-addressing hash of
+        # `hash_capacity` slots instead of a dense array over its key range
+        self.hash_capacity = None
+        if hash_capacity:
+            cap = 1
+            while cap < hash_capacity:
+                cap <<= 1
+            self.hash_capacity = cap
+            assert not bsp, "hash-backed (Map) tables add in place: use SSP or ASP"
+            assert dtype == torch.float32 and self.k == 1
         for s, (b, e) in enumerate(self.ranges):
             r = self.shard_owner[s]
-            nbytes = _align((e - b) * self.k * self.itemsize)
+            nbytes = _align((e - b) * self.k * self.itemsize) if not self.hash_capacity else _align(self.hash_capacity * 8)
             self.woff[s] = per_rank[r]
             per_rank[r] += nbytes
             if bsp:
@@ -104,7 +114,25 @@ class DeviceTable:
         v.vals_per_key = self.k
         v.dtype = _lib.F32 if dtype == torch.float32 else _lib.F64
         self.view = v
-        # view with adds forced in place (used by restore / init)
+        self.hview = None
+        if self.hash_capacity:
+            h = _lib.HashView()
+            for s in range(self.num_shards):
+                base = self.slab.ptrs[self.shard_owner[s]] + self.woff[s]
+                h.keys[s] = base
+                h.vals[s] = base + self.hash_capacity * 4
+                h.capacity[s] = self.hash_capacity
+                h.begin[s] = self.ranges[s][0]
+            h.begin[self.num_shards] = self.ranges[-1][1]
+            h.num_shards = self.num_shards
+            self.hview = h
+            self.overflow = torch.zeros(1, dtype=torch.int32, device=f"cuda:{self.device}")
+            for s in self.own_shards:
+                base = self.slab.local_ptr + self.woff[s]
+                _lib.check(self.lib.mps_hash_clear(C.c_void_p(base), C.c_void_p(base + self.hash_capacity * 4),
+                                                   self.hash_capacity, _lib.stream_ptr()), "hash_clear")
+            torch.cuda.synchronize(self.device)
+            control.barrier()
         self._timeout_s = float(os.environ.get("MINIPS_SPIN_TIMEOUT_S", "10"))
         self.num_workers = 1
         self._clock_view = None
@@ -144,6 +172,22 @@ class DeviceTable:
         off = self.soff[s] if staging else self.woff[s]
         return self.slab.local_tensor(off, (e - b) * self.k, self.dtype)
 
+    def hash_items(self, s: int):
+        """Live (keys, values) of a LOCAL hash shard, sorted by key."""
+        assert self.hash_capacity and self.shard_owner[s] == self.rank
+        dev = f"cuda:{self.device}"
+        keys = torch.empty(self.hash_capacity, dtype=torch.int32, device=dev)
+        vals = torch.empty(self.hash_capacity, dtype=torch.float32, device=dev)
+        count = torch.zeros(1, dtype=torch.int32, device=dev)
+        base = self.slab.local_ptr + self.woff[s]
+        _lib.check(self.lib.mps_hash_export(C.c_void_p(base), C.c_void_p(base + self.hash_capacity * 4),
+                                            self.hash_capacity, C.c_void_p(keys.data_ptr()), C.c_void_p(vals.data_ptr()),
+                                            C.c_void_p(count.data_ptr()), _lib.stream_ptr()), "hash_export")
+        n = int(count.item())
+        k64 = keys[:n].to(torch.int64) & 0xFFFFFFFF
+        order = torch.argsort(k64)
+        return k64[order], vals[:n][order]
+
     def pad_tensor(self) -> torch.Tensor:
         return self.slab.local_tensor(self.pad_off, _lib.PAD_INTS, torch.int32)
 
@@ -164,6 +208,9 @@ class DeviceTable:
             self.fold_clock = start_clock
 
     def check_error(self):
+        if self.hview is not None and int(self.overflow.item()) != 0:
+            raise RuntimeError(f"table {self.table_id}: a hash shard overflowed (capacity {self.hash_capacity}); "
+                               "create the table with a larger map_capacity")
         if int(self.pad_tensor()[_lib.PAD_ERROR].item()) != 0:
             raise RuntimeError(f"table {self.table_id}: device-side wait timed out "
                                f"(a peer did not reach the expected clock within {self._timeout_s}s)")
@@ -225,6 +272,10 @@ class KVClientTable:
             out = torch.empty(n * t.k, dtype=t.dtype, device=self.dev)
         self._local_gate()
         cv = t.clock_view()
+        if t.hview is not None:
+            _lib.check(self.lib.mps_hash_get(C.byref(t.hview), C.byref(cv), self.progress, C.c_void_p(k32.data_ptr()),
+                                             C.c_void_p(out.data_ptr()), n, self._sp()), "hash_get")
+            return out
         with torch.cuda.stream(self.stream):
             _lib.check(self.lib.mps_pull(C.byref(t.view), C.byref(cv), self.worker_id, self.progress,
                                          C.c_void_p(k32.data_ptr()), C.c_void_p(out.data_ptr()), n,
@@ -236,6 +287,10 @@ class KVClientTable:
         k32 = keys_as_i32(keys, self.dev)
         v = torch.as_tensor(vals).to(self.dev, dtype=t.dtype, non_blocking=True).contiguous()
         assert v.numel() == k32.numel() * t.k
+        if t.hview is not None:
+            _lib.check(self.lib.mps_hash_add(C.byref(t.hview), C.c_void_p(k32.data_ptr()), C.c_void_p(v.data_ptr()),
+                                             k32.numel(), C.c_void_p(t.overflow.data_ptr()), self._sp()), "hash_add")
+            return
         _lib.check(self.lib.mps_push(C.byref(t.view), C.c_void_p(k32.data_ptr()), C.c_void_p(v.data_ptr()),
                                      k32.numel(), self._sp()), "push")
         if self.stream is not None:
@@ -245,6 +300,7 @@ class KVClientTable:
     def get_all(self, out: Optional[torch.Tensor] = None) -> torch.Tensor:
         """Get of every key of the table (k-means centroids, LR eval) as slab copies."""
         t = self.table
+        assert t.hview is None, "whole-table Get needs dense (Vector) storage"
         if out is None:
             out = torch.empty(t.num_keys * t.k, dtype=t.dtype, device=self.dev)
         self._local_gate()

@@ -101,7 +101,7 @@ class Engine:
     def create_table(self, ranges: Optional[Sequence[Range]] = None, model_type: ModelType = ModelType.SSP,
                      storage_type: StorageType = StorageType.Vector, staleness: int = 0, *,
                      num_dims: Optional[int] = None, dtype: torch.dtype = torch.float32,
-                     vals_per_key: int = 1) -> int:
+                     vals_per_key: int = 1, map_capacity: Optional[int] = None) -> int:
         """Collective: call with identical arguments, in the same order, on every node."""
         assert self.started
         if ranges is None:
@@ -113,8 +113,11 @@ class Engine:
         owner = [node_ids.index(self.id_mapper.get_node_id_for_thread(t)) for t in server_tids]
         tid = self.model_count
         self.model_count += 1
+        # StorageType.Map over a bounded range behaves exactly like Vector (missing keys read 0, adds
+        # accumulate) and is stored densely unless map_capacity asks for real hash shards
         self.tables[tid] = DeviceTable(tid, ranges, owner, self.control, model_type, staleness, storage_type,
-                                       dtype, vals_per_key, self.device)
+                                       dtype, vals_per_key, self.device,
+                                       hash_capacity=map_capacity if storage_type == StorageType.Map else None)
         return tid
 
     CreateTable = create_table
