@@ -235,9 +235,32 @@ class Engine:
         if self.dump_callback:
             self.dump_callback()
 
-    def checkpoint_table(self, table_id: int, client: KVClientTable):
+    def checkpoint_table(self, table_id: int, client: Optional[KVClientTable] = None):
+        """KVClientTable::CheckPoint (kv_client_table.hpp:136-154).  Collective on this backend."""
         from ..utils import checkpoint as ckpt
         ckpt.dump_table(self, self.tables[table_id], client)
+
+    def restore_table(self, table_id: int) -> Dict[int, int]:
+        """Model Restore (ssp_model.cpp:127-137): reload shards + iteration map from the last dump."""
+        from ..utils import checkpoint as ckpt
+        it_map = ckpt.restore_table(self, self.tables[table_id])
+        self.iteration_map.update(it_map)
+        return it_map
+
+    def rollback(self) -> Dict[int, int]:
+        """Global rollback to the last checkpoint (comm/mailbox.cpp:172-190): every table is
+        restored; workers resume at the checkpointed iteration."""
+        out: Dict[int, int] = {}
+        for tid in sorted(self.tables):
+            if self.tables[tid].hview is None:
+                out = self.restore_table(tid)
+        return out
+
+    def set_iteration(self, worker_id: int, iteration: int):
+        self.iteration_map[worker_id] = iteration
+
+    def get_iteration(self, worker_id: int) -> int:
+        return self.iteration_map.get(worker_id, 0)
 
     # ---- convenience ----------------------------------------------------------------------------
     @classmethod

@@ -1,0 +1,133 @@
+"""Checkpoint / restore of device tables in the reference's dump formats.
+
+  <prefix>server_params_<id>    one line, "<local_idx>:<val> " for every non-zero entry of the
+                                shard, local_idx = key - range.begin   (server/vector_storage.hpp:54-73)
+  <prefix>server_progress_<id>  "min_clock:<v> <tid>:<v> ..."           (server/util/progress_tracker.hpp:68-85)
+  <prefix>worker_config_<id>    "<worker_id>:<iteration> ..."           (lib/svm_dumper.hpp:51-66)
+
+<id> is the node id; a node with several server shards appends ".<k>" for shards k >= 1.  Values are
+written with round-trip precision (the reference's 6 significant digits lose weights) and Restore
+parses what Dump wrote (the reference's Restore truncates to int).  Clocks / iterations are rounded
+to the checkpoint interval like the reference (checkpoints are taken every `interval` iterations).
+
+On the device backend CheckPoint() is COLLECTIVE: every worker of the task calls it at the same
+iteration (there are no server threads that could dump on a remote worker's request).
+"""
+from __future__ import annotations
+
+import os
+from typing import Dict, Optional
+
+import numpy as np
+import torch
+
+from ..ops import _lib
+
+
+def _paths(prefix: str, node_id: int, k: int, kind: str) -> str:
+    return f"{prefix}{kind}_{node_id}" + (f".{k}" if k else "")
+
+
+def _resolve(path: str) -> str:
+    """hdfs://host:port/a/b -> $MINIPS_HDFS_ROOT/a/b (same mapping as csrc/core/file_io.cpp)."""
+    if path.startswith("hdfs://"):
+        rest = path[7:]
+        tail = rest[rest.find("/"):] if "/" in rest else "/"
+        path = os.environ.get("MINIPS_HDFS_ROOT", "/tmp/minips_hdfs") + tail
+    d = os.path.dirname(path)
+    if d:
+        os.makedirs(d, exist_ok=True)
+    return path
+
+
+def round_to_interval(v: int, interval: int = 100) -> int:
+    return int(round(v / interval)) * interval if interval > 0 else v
+
+
+def write_sparse_line(path: str, values: np.ndarray):
+    """The VectorStorage::Dump format."""
+    idx = np.flatnonzero(values)
+    with open(_resolve(path), "w") as f:
+        step = 1 << 18
+        for s in range(0, idx.size, step):
+            chunk = idx[s:s + step]
+            f.write(" ".join(f"{i}:{values[i]:.9g}" for i in chunk))
+            f.write(" ")
+
+
+def read_sparse_line(path: str, size: int, dtype=np.float32) -> np.ndarray:
+    out = np.zeros(size, dtype=dtype)
+    p = _resolve(path)
+    if not os.path.exists(p):
+        return out
+    with open(p) as f:
+        for tok in f.read().split():
+            i, v = tok.split(":")
+            out[int(i)] = float(v)
+    return out
+
+
+def dump_table(engine, table, client=None, prefix: Optional[str] = None, interval: int = 100,
+               iteration_map: Optional[Dict[int, int]] = None):
+    """Collective, blocking dump of one table: shard values, progress tracker, iteration map."""
+    prefix = prefix if prefix is not None else str(engine.context.get("checkpoint_file_prefix", ""))
+    torch.cuda.synchronize(table.device)
+    engine.control.barrier()  # every push of every worker has landed
+    engine.run_dump_callback()
+    node_id = engine.node.id
+    for k, s in enumerate(table.own_shards):
+        if table.hview is not None:
+            keys, vals = table.hash_items(s)
+            lo = table.ranges[s][0]
+            with open(_resolve(_paths(prefix, node_id, k, "server_params")), "w") as f:
+                f.write(" ".join(f"{int(kk) - lo}:{float(v):.9g}" for kk, v in zip(keys.tolist(), vals.tolist())))
+                f.write(" ")
+            continue
+        # BSP: staging is empty between clock edges when called at an iteration boundary
+        vals = table.shard_tensor(s).detach().cpu().numpy()
+        write_sparse_line(_paths(prefix, node_id, k, "server_params"), vals)
+    pad = table.pad_tensor().cpu().numpy()
+    spec = engine.worker_spec
+    with open(_resolve(_paths(prefix, node_id, 0, "server_progress")), "w") as f:
+        prog = pad[_lib.PAD_PROGRESS:_lib.PAD_PROGRESS + table.num_workers]
+        f.write(f"min_clock:{round_to_interval(int(prog.min()) if prog.size else 0, interval)} ")
+        for w in range(table.num_workers):
+            tid = spec.worker_to_thread[w] if spec is not None and w in spec.worker_to_thread else w
+            f.write(f"{tid}:{round_to_interval(int(prog[w]), interval)} ")
+    it_map = iteration_map if iteration_map is not None else engine.iteration_map
+    with open(_resolve(_paths(prefix, node_id, 0, "worker_config")), "w") as f:
+        for w, it in sorted(it_map.items()):
+            f.write(f"{w}:{round_to_interval(int(it), interval)} ")
+    engine.control.barrier()
+
+
+def restore_table(engine, table, prefix: Optional[str] = None) -> Dict[int, int]:
+    """Collective restore of a table's shards + tracker; returns the iteration map."""
+    prefix = prefix if prefix is not None else str(engine.context.get("checkpoint_file_prefix", ""))
+    node_id = engine.node.id
+    dev = f"cuda:{table.device}"
+    assert table.hview is None, "restore of hash-backed tables goes through add()"
+    for k, s in enumerate(table.own_shards):
+        b, e = table.ranges[s]
+        vals = read_sparse_line(_paths(prefix, node_id, k, "server_params"), (e - b) * table.k,
+                                np.float32 if table.dtype == torch.float32 else np.float64)
+        table.shard_tensor(s).copy_(torch.from_numpy(vals).to(dev))
+        if table.model_type.name == "BSP":
+            table.shard_tensor(s, staging=True).zero_()
+    clock = 0
+    p = _resolve(_paths(prefix, node_id, 0, "server_progress"))
+    if os.path.exists(p):
+        for tok in open(p).read().split():
+            kname, v = tok.split(":")
+            if kname == "min_clock":
+                clock = int(v)
+    it_map: Dict[int, int] = {}
+    p = _resolve(_paths(prefix, node_id, 0, "worker_config"))
+    if os.path.exists(p):
+        for tok in open(p).read().split():
+            w, it = tok.split(":")
+            it_map[int(w)] = int(it)
+    torch.cuda.synchronize(table.device)
+    table.restored_clock = clock
+    engine.control.barrier()
+    return it_map
