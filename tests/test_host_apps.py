@@ -66,7 +66,7 @@ def test_lr_config1_localnodes(built, dataset, tmp_path, model):
     ck = str(tmp_path / "ck_")
     extra = [f"--input={dataset}", "--num_dims=1000", f"--kModelType={model}", "--kStaleness=2", "--batch_size=100",
              "--num_iters=150", "--num_workers_per_node=2", "--alpha=0.05", "--heartbeat_interval=-1",
-             "--block_size=65536", f"--assigner_master_port={base + 5}", "--checkpoint_toggle=true",
+             "--block_size=8192", f"--assigner_master_port={base + 5}", "--checkpoint_toggle=true",
              f"--checkpoint_file_prefix={ck}", "--checkpoint_interval=100"]
     rcs, outs = _launch(os.path.join(built, "lr_example"), hf, 3, extra)
     assert rcs == [0, 0, 0], outs
@@ -88,7 +88,7 @@ def test_lr_with_master_heartbeat(built, dataset, tmp_path):
     base = 25000 + os.getpid() % 2000
     hf = _hostfile(tmp_path, 3, base)
     extra = [f"--input={dataset}", "--num_dims=1000", "--kModelType=SSP", "--batch_size=50", "--num_iters=60",
-             "--num_workers_per_node=2", "--heartbeat_interval=1", "--block_size=65536",
+             "--num_workers_per_node=2", "--heartbeat_interval=1", "--block_size=8192",
              f"--assigner_master_port={base + 5}"]
     rcs, outs = _launch(os.path.join(built, "lr_example"), hf, 3, extra)
     assert rcs == [0, 0, 0], outs
@@ -100,7 +100,7 @@ def test_kmeans_two_nodes(built, dataset, tmp_path):
     base = 27000 + os.getpid() % 2000
     hf = _hostfile(tmp_path, 2, base)
     extra = [f"--input={dataset}", "--num_dims=1000", "--K=4", "--kmeans_init_mode=kmeans_parallel", "--num_iters=6",
-             "--batch_size=200", "--kModelType=BSP", "--block_size=65536", f"--assigner_master_port={base + 5}"]
+             "--batch_size=200", "--kModelType=BSP", "--block_size=8192", f"--assigner_master_port={base + 5}"]
     rcs, outs = _launch(os.path.join(built, "kmeans"), hf, 2, extra)
     assert rcs == [0, 0], outs
     assert "seeding took" in outs[0] and "SSE" in outs[0]
