@@ -130,6 +130,17 @@ class Engine:
 
     Barrier = barrier
 
+    def device_barrier(self, table_id: int, stream=None):
+        """Barrier among the ranks ON THE DEVICE (flags in the table's signal pad, no host round
+        trip): every rank's `stream` continues only after every rank enqueued its barrier.
+        Collective — all ranks must call it the same number of times."""
+        import ctypes as C
+        from ..ops import _lib
+        t = self.tables[table_id]
+        t.barrier_epoch += 1
+        cv = t.clock_view()
+        _lib.check(t.lib.mps_barrier(C.byref(cv), t.barrier_epoch, _lib.stream_ptr(stream)), "barrier")
+
     # ---- run (engine.cpp:246-297) ---------------------------------------------------------------
     def allocate_workers(self, worker_alloc: Sequence[WorkerAlloc]) -> WorkerSpec:
         spec = WorkerSpec(worker_alloc)

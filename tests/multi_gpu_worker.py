@@ -117,6 +117,20 @@ def main():
         for it, v in enumerate(vals):
             assert torch.all(v == float(2 * world * it)), (rank, wid, it, v[:4].tolist())
 
+    # ---- 6. device-side barrier: a flag written before the barrier by a peer is visible after it
+    t6 = engine.create_table(num_dims=1024, model_type=ModelType.ASP)
+
+    def bar_fn(info):
+        t = info.create_kv_client_table(t6)
+        for round_ in range(1, 4):
+            t.add(torch.tensor([rank]), torch.ones(1))
+            engine.device_barrier(t6)
+            got = t.get(torch.arange(world))
+            assert torch.all(got == float(round_)), (rank, round_, got.tolist())
+            engine.device_barrier(t6)
+
+    run_task(engine, [t6], bar_fn)
+
     engine.stop_everything()
     import torch.distributed as dist
     if dist.is_initialized():

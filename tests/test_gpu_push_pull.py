@@ -163,3 +163,15 @@ def test_multi_worker_bsp_lockstep(engine):
     for w in (0, 1):
         for it, v in enumerate(seen[w]):
             assert torch.all(v.cpu() == 2.0 * it), (w, it, v[:4])
+
+
+def test_device_barrier_single_rank(engine):
+    tid = engine.create_table(num_dims=64, model_type=ModelType.ASP)
+
+    def fn(info):
+        for _ in range(3):
+            engine.device_barrier(tid)
+        torch.cuda.synchronize()
+
+    _run(engine, tid, fn)
+    assert engine.tables[tid].barrier_epoch == 3
