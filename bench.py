@@ -41,6 +41,7 @@ def parse():
     ap.add_argument("--staleness", type=int, default=0)
     ap.add_argument("--alpha", type=float, default=0.01)
     ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--timeline", action="store_true", help="also print the in-kernel phase timeline (LR)")
     ap.add_argument("--e2e-steps", type=int, default=0, help="0 = same as --steps")
     return ap.parse_args()
 
@@ -132,6 +133,18 @@ def bench_lr_ours(args):
             result["h2d"] = loader.bytes_per_batch
             result["e2e_loss_last"] = float(hl[-1, 0]) / B
         result["clocks"] = sampler.stop()
+        if args.timeline:
+            # untimed extra run with the in-kernel phase timeline (rank 0 prints the means)
+            n_tl = 60
+            tl = torch.zeros(n_tl * 8, dtype=torch.int64, device=dev)
+            tr.train_dense(starts(n_tl).to(dev), B, timeline=tl)
+            torch.cuda.synchronize()
+            t = tl.view(n_tl, 8).cpu().double()
+            d = ((t[:, 1:6] - t[:, 0:5]) / 1e3)[5:].mean(0).tolist()
+            names = ["gate", "pull+sync1", "rows+sync2", "pulled-wait", "push+signal"]
+            if rank == 0:
+                print("timeline us (rank 0, CTA 0): " + ", ".join(f"{n}={v:.2f}" for n, v in zip(names, d)) +
+                      f", iter={((t[1:, 0] - t[:-1, 0]) / 1e3)[5:].mean().item():.2f}", file=sys.stderr)
 
     task = MLTask()
     task.set_worker_alloc([WorkerAlloc(n.id, 1) for n in engine.nodes])
