@@ -256,6 +256,20 @@ int mps_kmeans_delta(const float* centers, const float* counts_old, const float*
                      const float* counts_batch, int K, int D, float alpha, float* delta_c,
                      float* delta_n, void* stream);
 
+/* ---- dense logistic regression on tensor cores (csrc/kernels/dense_lr_tc.cu) ----------- */
+/* Forward of a dense batch (lr_example.cpp:293-305 for dense features): logits = X.w on
+ * tcgen05/TMEM fed by TMA, sigmoid / logloss / coef = alpha (y - p) fused in the TMEM epilogue,
+ * weight pull fused into the prologue (weights_view: fp32 table of D keys; or w_f32 local).
+ * x_bf16 [n, D] row-major, D % 8 == 0.  Scratch: w16_scratch 16 * roundup(D, 64) bf16,
+ * sync_ctr [1].  Outputs: coef [n], loss_out[0..1] += (logloss sum, #correct), optional
+ * w_f32_out [D]. */
+int mps_dense_lr_forward_tc(const MpsTableView* weights_view, const MpsClockView* clk, int progress,
+                            const float* w_f32, const void* x_bf16, const float* label, int64_t n, int D,
+                            float alpha, void* w16_scratch, float* w_f32_out, int* sync_ctr, float* coef,
+                            float* loss_out, int max_ctas, void* stream);
+/* Backward: grad[d] += sum_r coef[r] * x[r, d] (lr_example.cpp:305-312), feeds mps_push_dense. */
+int mps_dense_lr_grad(const void* x_bf16, const float* coef, int64_t n, int D, float* grad, void* stream);
+
 #ifdef __cplusplus
 }
 #endif
