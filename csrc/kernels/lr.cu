@@ -53,79 +53,83 @@ __device__ __forceinline__ void block_accumulate(float loss, float correct, floa
   __syncthreads();
 }
 
+template <int L>
+__device__ __forceinline__ float group_sum_sparse(float v, unsigned mask) {
+#pragma unroll
+  for (int o = L / 2; o > 0; o >>= 1) v += __shfl_xor_sync(mask, v, o);
+  return v;
+}
+
 // ------------------------------------------------------------------ sparse regime
+// L lanes per row (32/L rows in flight per warp), up to kSparseRegs non-zeros per lane held in
+// registers: all of a row's peer loads are issued before the first is consumed, and the same
+// registers feed the red.add pass.
+constexpr int kSparseRegs = 8;
+
+template <int L>
 __global__ void __launch_bounds__(256)
 lr_step_sparse_kernel(const __grid_constant__ MpsTableView v, const __grid_constant__ MpsClockView c,
                       int gated, int progress, const __grid_constant__ MpsCsr csr, int64_t row_begin,
                       int64_t batch, float alpha, float* __restrict__ loss_out) {
+  constexpr int E = kSparseRegs;
   if (gated) cta_gate(c, progress);
   const int lane = threadIdx.x & 31;
-  const int64_t warp = (static_cast<int64_t>(blockIdx.x) * blockDim.x + threadIdx.x) >> 5;
-  const int64_t nwarps = (static_cast<int64_t>(gridDim.x) * blockDim.x) >> 5;
+  const int gl = lane & (L - 1);
+  const unsigned mask = (L == 32) ? 0xffffffffu : (((1u << L) - 1u) << (lane & ~(L - 1)));
+  const int64_t group = (static_cast<int64_t>(blockIdx.x) * blockDim.x + threadIdx.x) / L;
+  const int64_t ngroups = (static_cast<int64_t>(gridDim.x) * blockDim.x) / L;
   float loss = 0.f, correct = 0.f;
-  for (int64_t r = warp; r < batch; r += nwarps) {
+  for (int64_t r = group; r < batch; r += ngroups) {
     int64_t ridx = row_begin + r;
     if (ridx >= csr.n_rows) ridx %= csr.n_rows;
     const int64_t beg = csr.row_ptr[ridx], end = csr.row_ptr[ridx + 1];
-    // pull + forward: two nnz per lane in flight (rows of <= 64 nnz stay in registers)
-    float x0 = 0.f, x1 = 0.f;
-    float* d0 = nullptr;
-    float* d1 = nullptr;
-    float acc = 0.f;
-    for (int64_t base = beg; base < end; base += 64) {
-      const int64_t j0 = base + lane, j1 = j0 + 32;
-      uint32_t kc0 = 0, kc1 = 0;
-      float kx0 = 0.f, kx1 = 0.f;
-      if (j0 < end) { kc0 = ld_stream(csr.col + j0); kx0 = ld_stream(csr.val + j0); }
-      if (j1 < end) { kc1 = ld_stream(csr.col + j1); kx1 = ld_stream(csr.val + j1); }
-      float* p0 = nullptr;
-      float* p1 = nullptr;
-      float w0 = 0.f, w1 = 0.f;
-      if (j0 < end) {
-        const int s = owner_of(v, kc0);
-        if (s >= 0) {
-          w0 = ld_sys(static_cast<const float*>(v.weights[s]) + (kc0 - v.begin[s]));
-          p0 = static_cast<float*>(v.staging[s] ? v.staging[s] : v.weights[s]) + (kc0 - v.begin[s]);
-        }
+    uint32_t off[E];
+    float x[E];
+    int sh[E];
+#pragma unroll
+    for (int e = 0; e < E; ++e) {
+      const int64_t j = beg + gl + e * L;
+      x[e] = 0.f;
+      sh[e] = -1;
+      off[e] = 0;
+      if (j < end) {
+        const uint32_t key = ld_stream(csr.col + j);
+        x[e] = ld_stream(csr.val + j);
+        sh[e] = owner_of(v, key);
+        if (sh[e] >= 0) off[e] = key - v.begin[sh[e]];
       }
-      if (j1 < end) {
-        const int s = owner_of(v, kc1);
-        if (s >= 0) {
-          w1 = ld_sys(static_cast<const float*>(v.weights[s]) + (kc1 - v.begin[s]));
-          p1 = static_cast<float*>(v.staging[s] ? v.staging[s] : v.weights[s]) + (kc1 - v.begin[s]);
-        }
-      }
-      acc = fmaf(w0, kx0, acc);
-      acc = fmaf(w1, kx1, acc);
-      if (base == beg) { x0 = kx0; x1 = kx1; d0 = p0; d1 = p1; }
     }
-    const float z = warp_sum(acc);
+    // pull + forward (Get fused with the SpMV): peer ld straight from the owning shard
+    float w[E];
+#pragma unroll
+    for (int e = 0; e < E; ++e) w[e] = sh[e] >= 0 ? ld_sys(static_cast<const float*>(v.weights[sh[e]]) + off[e]) : 0.f;
+    float acc = 0.f;
+#pragma unroll
+    for (int e = 0; e < E; ++e) acc = fmaf(w[e], x[e], acc);
+    for (int64_t j = beg + gl + E * L; j < end; j += L) {  // rows longer than L*E non-zeros
+      const uint32_t key = ld_stream(csr.col + j);
+      const int s2 = owner_of(v, key);
+      if (s2 >= 0) acc = fmaf(ld_sys(static_cast<const float*>(v.weights[s2]) + (key - v.begin[s2])), ld_stream(csr.val + j), acc);
+    }
+    const float z = group_sum_sparse<L>(acc, mask);
     const float y = csr.label[ridx];
     const float pred = sigmoidf_fast(z);
     const float g = alpha * (y - pred);
-    if (lane == 0) {
+    if (gl == 0) {
       loss += logloss(z, y);
       correct += ((pred > 0.5f) == (y > 0.5f)) ? 1.f : 0.f;
     }
-    // gradient + push: red.add at the owner (server/vector_storage.hpp:28-38)
-    if (d0 && x0 != 0.f) red_sys(d0, g * x0);
-    if (d1 && x1 != 0.f) red_sys(d1, g * x1);
-    for (int64_t base = beg + 64; base < end; base += 64) {
-      const int64_t j0 = base + lane, j1 = j0 + 32;
-      if (j0 < end) {
-        const uint32_t kc = ld_stream(csr.col + j0);
-        const float kx = ld_stream(csr.val + j0);
-        const int s = owner_of(v, kc);
-        if (s >= 0 && kx != 0.f)
-          red_sys(static_cast<float*>(v.staging[s] ? v.staging[s] : v.weights[s]) + (kc - v.begin[s]), g * kx);
-      }
-      if (j1 < end) {
-        const uint32_t kc = ld_stream(csr.col + j1);
-        const float kx = ld_stream(csr.val + j1);
-        const int s = owner_of(v, kc);
-        if (s >= 0 && kx != 0.f)
-          red_sys(static_cast<float*>(v.staging[s] ? v.staging[s] : v.weights[s]) + (kc - v.begin[s]), g * kx);
-      }
+    // gradient + push (Add fused): red.add at the owner (server/vector_storage.hpp:28-38)
+#pragma unroll
+    for (int e = 0; e < E; ++e)
+      if (sh[e] >= 0 && x[e] != 0.f)
+        red_sys(static_cast<float*>(v.staging[sh[e]] ? v.staging[sh[e]] : v.weights[sh[e]]) + off[e], g * x[e]);
+    for (int64_t j = beg + gl + E * L; j < end; j += L) {
+      const uint32_t key = ld_stream(csr.col + j);
+      const float kx = ld_stream(csr.val + j);
+      const int s2 = owner_of(v, key);
+      if (s2 >= 0 && kx != 0.f)
+        red_sys(static_cast<float*>(v.staging[s2] ? v.staging[s2] : v.weights[s2]) + (key - v.begin[s2]), g * kx);
     }
   }
   block_accumulate(loss, correct, loss_out);
@@ -430,11 +434,11 @@ int mps_lr_step_sparse(const MpsTableView* view, const MpsClockView* clk, int wo
   int dev = 0, sms = 148;
   cudaGetDevice(&dev);
   cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
-  int64_t want = (batch + 7) / 8;  // 8 warps (rows) per CTA
-  const int grid = static_cast<int>(want < sms * 8 ? want : sms * 8);
+  int64_t want = (batch + 31) / 32;  // 32 row groups of 8 lanes per 256-thread CTA
+  const int grid = static_cast<int>(want < 1 ? 1 : (want < sms * 8 ? want : sms * 8));
   MpsClockView c{};
   if (clk) c = *clk;
-  mps::lr_step_sparse_kernel<<<grid, 256, 0, static_cast<cudaStream_t>(stream)>>>(
+  mps::lr_step_sparse_kernel<8><<<grid, 256, 0, static_cast<cudaStream_t>(stream)>>>(
       *view, c, clk != nullptr, progress, *csr, row_begin, batch, alpha, loss_out);
   MPS_LAUNCH_CHECK();
   return 0;
