@@ -57,7 +57,9 @@ def run_reference(args):
     except Exception as e:  # noqa: BLE001
         emit({"impl": "reference", "unavailable": f"baseline/ref_run.py not importable: {e}"})
         return
-    emit(ref_run.run(args))
+    rec = ref_run.run(args)
+    if rec is not None:            # under torchrun only rank 0 reports
+        emit(rec)
 
 
 def base_record(args, world, metric, value, unit, ms_per_step, clocks, config, extra=None):
