@@ -79,7 +79,12 @@ def run_lr(args, ref_bin):
     if rank != 0:
         return None                       # rank 0 launches every reference process of the job
     n = max(1, int(os.environ.get("WORLD_SIZE", args.gpus)))
-    steps, warm = args.steps, max(3, args.warmup)
+    n_req = n
+    warm = max(3, args.warmup)
+    # the reference's gradient loop scans the batch's whole key list once per row (lr_example.cpp:299-311),
+    # so a step costs seconds at these batch sizes: bound the number of timed iterations per run
+    cap = int(os.environ.get("MINIPS_REF_MAX_STEPS", 0)) or {1: 100, 2: 60}.get(n_req, 30)
+    steps = min(args.steps, cap)
     rows = int(os.environ.get("MINIPS_REF_SAMPLES", args.samples))
     features = args.features
     gen = os.path.join(os.path.dirname(ref_bin), "gen_libsvm")
@@ -87,13 +92,16 @@ def run_lr(args, ref_bin):
     n_gpus = n
     n = int(os.environ.get("MINIPS_REF_NODES", N_SHARDS))        # reference node processes
     servers = 1
-    wpn = int(os.environ.get("MINIPS_REF_WORKERS_PER_NODE", 0)) or max(1, min(16, (cores - 2) // n - servers))
+    # that scan makes the work per step fall with the number of workers the batch is split over (rows per
+    # worker x keys per worker), so many worker threads per node is the reference's best setting even when
+    # they outnumber the cores
+    wpn = int(os.environ.get("MINIPS_REF_WORKERS_PER_NODE", 0)) or min(8 * n_gpus, 32)
     global_batch = n_gpus * args.batch
     while global_batch % (n * wpn):
         wpn -= 1
     batch = global_batch // (n * wpn)
     load_threads = max(1, min(4, cores // n))
-    limit = float(os.environ.get("MINIPS_REF_TIMEOUT", 1500))
+    limit = float(os.environ.get("MINIPS_REF_TIMEOUT", 900))
 
     t_gen = time.time()
     data = _dataset(gen, rows, features, NNZ_PER_ROW)
@@ -182,7 +190,7 @@ def run_lr(args, ref_bin):
     value = global_batch / (ms_per_step / 1e3)
     return {
         "metric": "sparse_lr_samples_per_sec", "value": value, "unit": "samples/s", "n_gpus": n_gpus,
-        "steps": steps, "warmup": warm, "ms_per_step": ms_per_step, "higher_is_better": True,
+        "steps": steps, "steps_requested": args.steps, "warmup": warm, "ms_per_step": ms_per_step, "higher_is_better": True,
         "scaling": "weak", "vs_baseline": None, "dtype": "fp64 parameters (reference KVClientTable<double>), fp32 features",
         "data": "synthetic", "impl": "reference",
         "config": {
