@@ -83,8 +83,11 @@ def run_lr(args, ref_bin):
     warm = max(3, args.warmup)
     # the reference's gradient loop scans the batch's whole key list once per row (lr_example.cpp:299-311),
     # so a step costs seconds at these batch sizes: bound the number of timed iterations per run
-    cap = int(os.environ.get("MINIPS_REF_MAX_STEPS", 0)) or {1: 100, 2: 60}.get(n_req, 30)
-    steps = min(args.steps, cap)
+    cap = int(os.environ.get("MINIPS_REF_MAX_STEPS", 0)) or {1: 90, 2: 60}.get(n_req, 30)
+    # and never reach iteration 100: worker 0 then calls table->CheckPoint() unconditionally
+    # (lr_example.cpp:320-331), and with checkpoint_toggle=false the servers never answer it
+    warm = min(warm, 10)
+    steps = min(args.steps, cap, 100 - warm)
     rows = int(os.environ.get("MINIPS_REF_SAMPLES", args.samples))
     features = args.features
     gen = os.path.join(os.path.dirname(ref_bin), "gen_libsvm")
