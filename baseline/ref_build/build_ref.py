@@ -35,10 +35,11 @@ def main():
     flags = ["-std=c++11", os.environ.get("MINIPS_REF_OPT", "-O2"), "-w", "-pthread", "-DHAS_HADOOP", "-include", "cstdint", "-include", "cstring", "-include", "string",
              "-include", "functional", "-include", "memory", "-include", "algorithm", "-include", "fcntl.h", f"-I{os.path.join(HERE, 'shims')}", f"-I{REF}"]
     dirs = ["base", "comm", "driver", "server", "worker", "master", "io"]
-    srcs = []
+    srcs, tests = [], []
     for d in dirs:
         for p in sorted(glob.glob(os.path.join(REF, d, "**", "*.cpp"), recursive=True)):
             if p.endswith("_test.cpp"):
+                tests.append(p)
                 continue
             srcs.append(p)
     apps = {"LRExample": os.path.join(REF, "apps/logistic_regression/lr_example.cpp"),
@@ -48,16 +49,19 @@ def main():
     def obj_of(src):
         return os.path.join(OUT, "obj", os.path.relpath(src, REF).replace("/", "_")[:-4] + ".o")
 
+    shim_mtime = max(os.path.getmtime(p) for p in glob.glob(os.path.join(HERE, "shims", "**", "*.h*"), recursive=True))
+
     def compile_one(src):
         o = obj_of(src)
-        if os.path.exists(o) and os.path.getmtime(o) > os.path.getmtime(src):
+        if os.path.exists(o) and os.path.getmtime(o) > max(os.path.getmtime(src), shim_mtime):
             return src, 0, ""
         p = subprocess.run([CXX, *flags, "-c", src, "-o", o], capture_output=True, text=True)
         return src, p.returncode, p.stderr
 
     failed = False
     with cf.ThreadPoolExecutor(max_workers=8) as ex:
-        for src, rc, err in ex.map(compile_one, srcs + list(apps.values())):
+        tests.append(os.path.join(REF, "test", "test_main.cpp"))
+        for src, rc, err in ex.map(compile_one, srcs + list(apps.values()) + tests):
             if rc:
                 failed = True
                 sys.stderr.write(f"--- {src}\n{err[:6000]}\n")
@@ -72,6 +76,14 @@ def main():
             sys.stderr.write(p.stderr[:6000])
             raise SystemExit(f"link of {name} failed")
         print("built", exe)
+    # the reference's own unit tests (HuskyUnitTest in its CMake build) under the gtest shim
+    exe = os.path.join(OUT, "bin", "RefUnitTest")
+    p = subprocess.run([CXX, "-pthread", *[obj_of(t) for t in tests], *objs, libzmq, f"-Wl,-rpath,{libdir}", "-o", exe],
+                       capture_output=True, text=True)
+    if p.returncode:
+        sys.stderr.write(p.stderr[:6000])
+        raise SystemExit("link of RefUnitTest failed")
+    print("built", exe)
     gen = os.path.join(OUT, "bin", "gen_libsvm")
     p = subprocess.run([CXX, "-std=c++17", "-O2", "-pthread", os.path.join(HERE, "gen_libsvm.cpp"), "-o", gen],
                        capture_output=True, text=True)
