@@ -44,10 +44,13 @@ def main():
             srcs.append(p)
     apps = {"LRExample": os.path.join(REF, "apps/logistic_regression/lr_example.cpp"),
             "KMeans": os.path.join(REF, "apps/kmeans/kmeans.cpp"),
-            "BasicExample": os.path.join(REF, "apps/basic/basic_example.cpp")}
+            "BasicExample": os.path.join(REF, "apps/basic/basic_example.cpp"),
+            # our own microbenchmark program against the reference library (config 5 baseline)
+            "RefPushPull": os.path.join(HERE, "ref_push_pull.cpp")}
 
     def obj_of(src):
-        return os.path.join(OUT, "obj", os.path.relpath(src, REF).replace("/", "_")[:-4] + ".o")
+        rel = os.path.relpath(src, REF) if src.startswith(REF) else "own_" + os.path.basename(src)
+        return os.path.join(OUT, "obj", rel.replace("/", "_")[:-4] + ".o")
 
     shim_mtime = max(os.path.getmtime(p) for p in glob.glob(os.path.join(HERE, "shims", "**", "*.h*"), recursive=True))
 
