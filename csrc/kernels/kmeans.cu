@@ -66,6 +66,67 @@ kmeans_delta_kernel(const float* __restrict__ centers, const float* __restrict__
   }
 }
 
+// Centroid normalisation FUSED with the push of both tables (kmeans.cpp:247-274: the delta of every
+// touched centre and its count, then Add + Add): one warp per centre row.  The old counts are read
+// straight from the owning shard (the Get of the counts table, kmeans.cpp:224, under its consistency
+// gate), the deltas go out as red.add into the owner's staging (BSP) or weights (SSP/ASP), and the
+// batch accumulators are cleared for the next iteration, so no delta buffer and no separate
+// pull / push / memset launch exists.
+__global__ void __launch_bounds__(256)
+kmeans_delta_push_kernel(const __grid_constant__ MpsTableView vc, const __grid_constant__ MpsTableView vn,
+                         const __grid_constant__ MpsClockView cn, int gated, int progress,
+                         const float* __restrict__ centers, float* __restrict__ sums,
+                         float* __restrict__ counts_batch, int K, int D, float alpha) {
+  if (gated) cta_gate(cn, progress);
+  const int lane = threadIdx.x & 31;
+  const int warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+  const int nwarps = (gridDim.x * blockDim.x) >> 5;
+  for (int c = warp; c < K; c += nwarps) {
+    const float m = counts_batch[c];
+    if (m <= 0.f) continue;  // untouched centre: its sums row is still zero
+    const uint32_t nkey = vn.begin[0] + static_cast<uint32_t>(c);
+    const int sn = owner_of(vn, nkey);
+    float n_old = 0.f;
+    if (lane == 0) n_old = ld_sys(static_cast<const float*>(vn.weights[sn]) + (nkey - vn.begin[sn]));
+    n_old = __shfl_sync(0xffffffffu, n_old, 0);
+    const float scale = alpha / (n_old + m);
+    for (int j = lane * 4; j < D; j += 128) {
+      const int64_t f = static_cast<int64_t>(c) * D + j;
+      const float4 s4 = *reinterpret_cast<const float4*>(sums + f);
+      const float4 c4 = *reinterpret_cast<const float4*>(centers + f);
+      float4 d;
+      d.x = scale * (s4.x - m * c4.x);
+      d.y = scale * (s4.y - m * c4.y);
+      d.z = scale * (s4.z - m * c4.z);
+      d.w = scale * (s4.w - m * c4.w);
+      *reinterpret_cast<float4*>(sums + f) = make_float4(0.f, 0.f, 0.f, 0.f);
+      // D % 4 == 0 and shard boundaries of the centre table fall on multiples of 4 values only when
+      // the ranges do; route per element when the chunk straddles or is misaligned in its shard
+      const uint32_t key0 = vc.begin[0] + static_cast<uint32_t>(f);
+      const int sc = owner_of(vc, key0);
+      const int64_t off = static_cast<int64_t>(key0) - vc.begin[sc];
+      float* base = static_cast<float*>(vc.staging[sc] ? vc.staging[sc] : vc.weights[sc]);
+      if (key0 + 4 <= vc.begin[sc + 1] && (off & 3) == 0) {
+        if (d.x != 0.f || d.y != 0.f || d.z != 0.f || d.w != 0.f) red_sys_v4(base + off, d);
+      } else {
+        const float dv[4] = {d.x, d.y, d.z, d.w};
+        for (int e = 0; e < 4; ++e) {
+          const uint32_t key = key0 + e;
+          const int se = owner_of(vc, key);
+          float* be = static_cast<float*>(vc.staging[se] ? vc.staging[se] : vc.weights[se]);
+          if (dv[e] != 0.f) red_sys(be + (key - vc.begin[se]), dv[e]);
+        }
+      }
+    }
+    __syncwarp();
+    if (lane == 0) {
+      float* nb = static_cast<float*>(vn.staging[sn] ? vn.staging[sn] : vn.weights[sn]);
+      red_sys(nb + (nkey - vn.begin[sn]), m);
+      counts_batch[c] = 0.f;
+    }
+  }
+}
+
 }  // namespace mps
 
 extern "C" {
@@ -94,6 +155,39 @@ int mps_kmeans_delta(const float* centers, const float* counts_old, const float*
                                                                                delta_n);
   MPS_LAUNCH_CHECK();
   return 0;
+}
+
+int mps_kmeans_delta_push(const MpsTableView* centers_view, const MpsTableView* counts_view,
+                          const MpsClockView* counts_clk, int progress, const float* centers, float* sums,
+                          float* counts_batch, int K, int D, float alpha, void* stream) {
+  if (D % 4 != 0 || centers_view->dtype != MPS_F32 || counts_view->dtype != MPS_F32 ||
+      centers_view->vals_per_key != 1 || counts_view->vals_per_key != 1)
+    return static_cast<int>(cudaErrorInvalidValue);
+  const int grid = (K + 7) / 8;  // 8 warps per CTA, one centre row per warp
+  MpsClockView none{};
+  mps::kmeans_delta_push_kernel<<<grid, 256, 0, static_cast<cudaStream_t>(stream)>>>(
+      *centers_view, *counts_view, counts_clk ? *counts_clk : none, counts_clk != nullptr, progress, centers, sums,
+      counts_batch, K, D, alpha);
+  MPS_LAUNCH_CHECK();
+  return 0;
+}
+
+int mps_kmeans_step(const MpsTableView* centers_view, const MpsClockView* centers_clk,
+                    const MpsTableView* counts_view, const MpsClockView* counts_clk, int worker, int progress,
+                    int fold, const void* x_bf16, int64_t n, int K, int D, float alpha,
+                    void* centers_bf16_scratch, float* cnorm_scratch, float* centers_f32, int* sync_ctr,
+                    int32_t* assign, float* dist, float* sums, float* counts_batch, float* sse, void* stream) {
+  int rc = mps_kmeans_assign_tc(centers_view, centers_clk, progress, nullptr, x_bf16, n, K, D, centers_bf16_scratch,
+                                cnorm_scratch, centers_f32, sync_ctr, assign, dist, 0, stream);
+  if (rc) return rc;
+  rc = mps_kmeans_accumulate(x_bf16, assign, dist, n, K, D, sums, counts_batch, sse, stream);
+  if (rc) return rc;
+  rc = mps_kmeans_delta_push(centers_view, counts_view, counts_clk, progress, centers_f32, sums, counts_batch, K, D,
+                             alpha, stream);
+  if (rc) return rc;
+  rc = mps_clock(centers_view, centers_clk, worker, progress + 1, fold, stream);
+  if (rc) return rc;
+  return mps_clock(counts_view, counts_clk, worker, progress + 1, fold, stream);
 }
 
 }  // extern "C"

@@ -255,6 +255,23 @@ int mps_kmeans_accumulate(const void* x_bf16, const int32_t* assign, const float
 int mps_kmeans_delta(const float* centers, const float* counts_old, const float* sums,
                      const float* counts_batch, int K, int D, float alpha, float* delta_c,
                      float* delta_n, void* stream);
+/* The same normalisation fused with the Get of the counts table and the Add of BOTH tables
+ * (kmeans.cpp:224, 247-274): old counts are read from the owning shards under counts_clk's gate
+ * (NULL = ungated), delta_c / delta_n go out as red.add to the owners (staging under BSP), and
+ * sums / counts_batch are cleared for the next batch.  centers: the fp32 centres this batch was
+ * assigned against (centers_f32_out of mps_kmeans_assign_tc).  f32 tables, D % 4 == 0. */
+int mps_kmeans_delta_push(const MpsTableView* centers_view, const MpsTableView* counts_view,
+                          const MpsClockView* counts_clk, int progress, const float* centers,
+                          float* sums, float* counts_batch, int K, int D, float alpha, void* stream);
+/* One whole mini-batch iteration of a worker (kmeans.cpp:216-275) enqueued by a single host call:
+ * assign (centre pull fused) -> accumulate -> delta + push of both tables -> Clock of both tables at
+ * progress + 1 (fold: this worker is the last local one to clock, see mps_clock). */
+int mps_kmeans_step(const MpsTableView* centers_view, const MpsClockView* centers_clk,
+                    const MpsTableView* counts_view, const MpsClockView* counts_clk, int worker,
+                    int progress, int fold, const void* x_bf16, int64_t n, int K, int D, float alpha,
+                    void* centers_bf16_scratch, float* cnorm_scratch, float* centers_f32, int* sync_ctr,
+                    int32_t* assign, float* dist, float* sums, float* counts_batch, float* sse,
+                    void* stream);
 
 /* ---- dense logistic regression on tensor cores (csrc/kernels/dense_lr_tc.cu) ----------- */
 /* Forward of a dense batch (lr_example.cpp:293-305 for dense features): logits = X.w on

@@ -17,6 +17,7 @@ import torch
 
 from ..ops import _lib
 from ..parallel.device_table import KVClientTable
+from ..parallel.types import ModelType
 
 
 def make_blobs(n: int, d: int, k_true: int, device="cuda", seed: int = 0, spread: float = 0.15,
@@ -102,6 +103,7 @@ class KMeansTrainer:
         self.delta_n = torch.empty(K, dtype=torch.float32, device=self.dev)
         self.counts_old = torch.empty(K, dtype=torch.float32, device=self.dev)
         self._out = None
+        self.allow_fused = True      # False forces the call-by-call path (tests, debugging)
 
     def step(self, start: int, batch: int, sse: Optional[torch.Tensor] = None) -> torch.Tensor:
         """One iteration on rows [start, start+batch).  Returns the 1-element SSE tensor."""
@@ -112,6 +114,9 @@ class KMeansTrainer:
                          torch.empty(n, dtype=torch.float32, device=self.dev))
         if sse is None:
             sse = torch.zeros(1, dtype=torch.float32, device=self.dev)
+        if self._fusable():
+            return self._step_fused(xb, n, sse)
+        # generic path (several local workers share the tables, or non-f32 tables):
         # Get of both tables: counts as a slab pull, centres inside the GEMM kernel
         self.tn.get_all(out=self.counts_old)
         assign, dist = self.assigner.assign(xb, client=self.tc, out=self._out)
@@ -131,6 +136,42 @@ class KMeansTrainer:
         self.tc.clock()
         self.tn.add_all(self.delta_n)
         self.tn.clock()
+        return sse
+
+    def _fusable(self) -> bool:
+        tc, tn = self.tc.table, self.tn.table
+        return (self.allow_fused and len(tc.local_workers) <= 1 and len(tn.local_workers) <= 1 and tc.dtype == torch.float32
+                and tn.dtype == torch.float32 and tc.hview is None and tn.hview is None
+                and tc.model_type == tn.model_type and self.tc.progress == self.tn.progress
+                and self.tc.stream is self.tn.stream)
+
+    def _step_fused(self, xb: torch.Tensor, n: int, sse: torch.Tensor) -> torch.Tensor:
+        """The whole iteration as ONE host call (mps_kmeans_step): assign with the centre pull fused ->
+        accumulate -> normalise + push of both tables fused -> Clock of both tables.  `sums` / `cnt`
+        are cleared by the kernel that consumes them, so nothing else is launched."""
+        tc, tn = self.tc.table, self.tn.table
+        a = self.assigner
+        assign, dist = self._out
+        progress = self.tc.progress
+        fold = int(tc.model_type == ModelType.BSP)        # the kernel skips the fold where a rank owns no shard
+        s = self.tc.stream or torch.cuda.current_stream()
+        with tc.lock, tn.lock:
+            _lib.check(self.lib.mps_kmeans_step(
+                C.byref(tc.view), C.byref(tc.clock_view()), C.byref(tn.view), C.byref(tn.clock_view()),
+                self.tc.worker_id, progress, fold, C.c_void_p(xb.data_ptr()), n, self.K, self.D, self.alpha,
+                C.c_void_p(a.c_bf16.data_ptr()), C.c_void_p(a.cnorm.data_ptr()), C.c_void_p(a.c_f32.data_ptr()),
+                C.c_void_p(a.sync.data_ptr()), C.c_void_p(assign.data_ptr()), C.c_void_p(dist.data_ptr()),
+                C.c_void_p(self.sums.data_ptr()), C.c_void_p(self.cnt.data_ptr()), C.c_void_p(sse.data_ptr()),
+                self.tc._sp()), "kmeans_step")
+            ev = torch.cuda.Event()
+            ev.record(s)
+            for t, cl in ((tc, self.tc), (tn, self.tn)):
+                t.local_clock[cl.worker_id] = progress + 1
+                t.local_events[cl.worker_id] = ev
+                if fold and t.own_count > 0:
+                    t.fold_clock = progress + 1
+                t.lock.notify_all()
+                cl.progress = progress + 1
         return sse
 
 

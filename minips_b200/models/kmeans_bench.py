@@ -42,6 +42,8 @@ def run(args, emit):
         tc.clock()
         tn.clock()
         tr = KMeansTrainer(tc, tn, x, K, alpha=1.0)
+        # fused: assign(+pull) / accumulate / delta+push / clock x2 from one host call; else call by call
+        res["launches_per_step"] = 5 if tr._fusable() else 10
         starts = torch.randint(0, max(1, n_local - B), (warm + steps,), generator=g).tolist()
         sse = torch.zeros(1, device=dev)
         for s in starts[:warm]:
@@ -122,7 +124,7 @@ def run(args, emit):
                    "l2_policy": f"inputs larger than L2: every step reads a fresh {B * D * 2 / 1e6:.0f} MB batch of a "
                                 f"{n_local * D * 2 / 1e9:.1f} GB per-GPU dataset",
                    "sse_per_point_first": res["sse_first"], "sse_per_point_last": res["sse_last"]},
-        "clocks": res["clocks"], "gpu_launches": 8 * steps,
+        "clocks": res["clocks"], "gpu_launches": res["launches_per_step"] * steps,
     }
     if "e2e_ms" in res:
         rec["e2e"] = {"value": world * B * steps / (res["e2e_ms"] / 1e3), "unit": "samples/s",

@@ -131,6 +131,39 @@ def main():
 
     run_task(engine, [t6], bar_fn)
 
+    # ---- 7. k-means under BSP: fused step (centre pull in the GEMM kernel, delta + push of both tables in one
+    #         kernel) on every rank against the batched oracle over all ranks' batches
+    from minips_b200.models.kmeans import KMeansTrainer, init_random, make_blobs, oracle_step, _min_sqdist
+    K7, D7, n7, b7, it7 = 128, 128, 16384, 4096, 3
+    xs = [make_blobs(n7, D7, K7, device=dev, seed=50 + r, spread=0.05) for r in range(world)]
+    t7c = engine.create_table(num_dims=K7 * D7, model_type=ModelType.BSP)
+    t7n = engine.create_table(num_dims=K7, model_type=ModelType.BSP)
+    c0 = init_random(xs[0], K7, seed=1)
+    out7 = {}
+
+    def km_fn(info):
+        tc, tn = info.create_kv_client_table(t7c), info.create_kv_client_table(t7n)
+        if rank == 0:
+            tc.add_all(c0.reshape(-1).contiguous())
+        tc.clock()
+        tn.clock()
+        tr = KMeansTrainer(tc, tn, xs[rank], K7, 1.0)
+        assert tr._fusable()
+        for i in range(it7):
+            tr.step(i * b7, b7)
+        out7["c"] = tc.get_all().view(K7, D7).clone()
+        out7["n"] = tn.get_all().clone()
+
+    run_task(engine, [t7c, t7n], km_fn)
+    c_ref, n_ref = c0.clone(), torch.zeros(K7, device=dev)
+    for i in range(it7):
+        c_ref, n_ref, _ = oracle_step(c_ref, n_ref, [x[i * b7:(i + 1) * b7] for x in xs], 1.0)
+    assert out7["n"].sum().item() == world * it7 * b7, (rank, out7["n"].sum().item())
+    allx = torch.cat(xs)
+    cost_dev, cost_ref = _min_sqdist(allx, out7["c"]).mean().item(), _min_sqdist(allx, c_ref).mean().item()
+    assert abs(cost_dev - cost_ref) <= 2e-2 * cost_ref + 1e-3, (rank, cost_dev, cost_ref)
+    assert (out7["n"] - n_ref).abs().sum().item() <= 0.05 * world * it7 * b7
+
     engine.stop_everything()
     import torch.distributed as dist
     if dist.is_initialized():

@@ -63,8 +63,9 @@ def test_assign_tc_few_ctas_many_groups():
     _check_objective(assign, dist, d_full)
 
 
+@pytest.mark.parametrize("fused", [True, False])
 @pytest.mark.parametrize("model", [ModelType.BSP, ModelType.SSP])
-def test_kmeans_training_matches_oracle(model):
+def test_kmeans_training_matches_oracle(model, fused):
     from minips_b200.models.kmeans import KMeansTrainer, init_random, make_blobs, oracle_step
     from minips_b200.parallel.engine import Engine
     K, D, n, batch, iters, alpha = 128, 128, 40_000, 8192, 4, 1.0
@@ -85,6 +86,8 @@ def test_kmeans_training_matches_oracle(model):
             tc.clock()
             tn.clock()
             tr = KMeansTrainer(tc, tn, x, K, alpha)
+            tr.allow_fused = fused
+            assert tr._fusable() == fused
             sses = [tr.step(i * batch, batch).clone() for i in range(iters)]
             out["centers"] = tc.get_all().view(K, D)
             out["counts"] = tn.get_all()
