@@ -133,7 +133,8 @@ def main():
 
     # ---- 7. k-means under BSP: fused step (centre pull in the GEMM kernel, delta + push of both tables in one
     #         kernel) on every rank against the batched oracle over all ranks' batches
-    from minips_b200.models.kmeans import KMeansTrainer, init_random, make_blobs, oracle_step, _min_sqdist
+    from minips_b200.models.kmeans import KMeansTrainer, init_random, make_blobs, _min_sqdist
+    from minips_b200.models.kmeans import oracle_step as km_oracle_step
     K7, D7, n7, b7, it7 = 128, 128, 16384, 4096, 3
     xs = [make_blobs(n7, D7, K7, device=dev, seed=50 + r, spread=0.05) for r in range(world)]
     t7c = engine.create_table(num_dims=K7 * D7, model_type=ModelType.BSP)
@@ -157,7 +158,7 @@ def main():
     run_task(engine, [t7c, t7n], km_fn)
     c_ref, n_ref = c0.clone(), torch.zeros(K7, device=dev)
     for i in range(it7):
-        c_ref, n_ref, _ = oracle_step(c_ref, n_ref, [x[i * b7:(i + 1) * b7] for x in xs], 1.0)
+        c_ref, n_ref, _ = km_oracle_step(c_ref, n_ref, [x[i * b7:(i + 1) * b7] for x in xs], 1.0)
     assert out7["n"].sum().item() == world * it7 * b7, (rank, out7["n"].sum().item())
     allx = torch.cat(xs)
     cost_dev, cost_ref = _min_sqdist(allx, out7["c"]).mean().item(), _min_sqdist(allx, c_ref).mean().item()
