@@ -105,6 +105,19 @@ def run_lr(args, ref_bin):
     batch = global_batch // (n * wpn)
     load_threads = max(1, min(4, cores // n))
     limit = float(os.environ.get("MINIPS_REF_TIMEOUT", 900))
+    # memory: every reference worker thread deep-copies its node's samples (BatchDataSampler's constructor,
+    # lib/batch_data_sampler.cpp:28-32: `data_ = data`), ~800 B per 40-nnz row, so the job needs about
+    # rows x 800 B x (workers_per_node + 1).  Keep that under 45 % of the free host memory by loading fewer
+    # rows of the same distribution (batches are random windows, so the step cost does not depend on it).
+    rows_requested = rows
+    try:
+        with open("/proc/meminfo") as f:
+            avail = next(int(l.split()[1]) * 1024 for l in f if l.startswith("MemAvailable"))
+    except (OSError, StopIteration):
+        avail = 64 << 30
+    rows_fit = int(0.45 * avail / (800 * (wpn + 1)))
+    if "MINIPS_REF_SAMPLES" not in os.environ and rows > rows_fit:
+        rows = max(200_000, rows_fit // 100_000 * 100_000)
 
     t_gen = time.time()
     data = _dataset(gen, rows, features, NNZ_PER_ROW)
@@ -117,7 +130,7 @@ def run_lr(args, ref_bin):
     with open(cfg, "w") as f:
         for i, node in enumerate([0, 1] + ids[1:]):
             f.write(f"{node}:localhost:{ports[i]}\n")
-    hb = 5
+    hb = 20          # a node counts as failed after 3 intervals: leave room for 250+ busy threads per box
     common = [
         f"--config_file={cfg}", "--hdfs_namenode=localhost", "--hdfs_namenode_port=9000",
         f"--input=hdfs://{data}", f"--kModelType={args.model}", "--kStorageType=Vector",
@@ -197,7 +210,7 @@ def run_lr(args, ref_bin):
         "scaling": "weak", "vs_baseline": None, "dtype": "fp64 parameters (reference KVClientTable<double>), fp32 features",
         "data": "synthetic", "impl": "reference",
         "config": {
-            "model": "sparse_logistic_regression", "samples": rows, "features": features, "nnz_per_row": NNZ_PER_ROW,
+            "model": "sparse_logistic_regression", "samples": rows, "samples_requested": rows_requested, "features": features, "nnz_per_row": NNZ_PER_ROW,
             "server_shards": servers * n, "consistency": args.model, "staleness": args.staleness,
             "global_batch": global_batch, "seq_len": None,
             "parallelism": f"{n} reference node processes on this box x ({wpn} worker + {servers} server thread(s)) "
