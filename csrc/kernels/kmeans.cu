@@ -50,6 +50,160 @@ kmeans_accumulate_kernel(const __nv_bfloat16* __restrict__ x, const int32_t* __r
   }
 }
 
+// ---- sorted accumulation -----------------------------------------------------------------
+// The kernel above issues one red.add.v4 per point and lane (32 M L2 atomics for a 1 M-point batch),
+// which costs as much as the distance GEMM.  The sorted path groups the batch by centre first
+// (counting sort of the row indices: histogram -> scan -> scatter), then every warp walks a run of
+// 64 consecutive sorted rows with the partial sum of the current centre in registers and issues one
+// red.add.v4 per lane only when the centre changes: HBM-bound row gathers instead of atomics.
+__global__ void __launch_bounds__(256)
+kmeans_hist_kernel(const int32_t* __restrict__ assign, int64_t n, int K, int* __restrict__ hist) {
+  extern __shared__ int sh[];
+  for (int c = threadIdx.x; c < K; c += blockDim.x) sh[c] = 0;
+  __syncthreads();
+  const int64_t chunk = (n + gridDim.x - 1) / gridDim.x;
+  const int64_t lo = chunk * blockIdx.x, hi = (lo + chunk < n) ? lo + chunk : n;
+  for (int64_t i = lo + threadIdx.x; i < hi; i += blockDim.x) {
+    const int a = assign[i];
+    if (a >= 0 && a < K) atomicAdd(&sh[a], 1);
+  }
+  __syncthreads();
+  for (int c = threadIdx.x; c < K; c += blockDim.x)
+    if (sh[c]) atomicAdd(&hist[c], sh[c]);
+}
+
+// one CTA: base[c] = exclusive prefix of hist, cursor = base, counts[c] += hist[c], hist cleared
+__global__ void __launch_bounds__(1024)
+kmeans_scan_kernel(int* __restrict__ hist, int K, int* __restrict__ base, int* __restrict__ cursor,
+                   float* __restrict__ counts) {
+  __shared__ int warp_tot[32];
+  __shared__ int carry;
+  if (threadIdx.x == 0) carry = 0;
+  __syncthreads();
+  const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+  for (int c0 = 0; c0 < K; c0 += blockDim.x) {
+    const int c = c0 + threadIdx.x;
+    const int h = c < K ? hist[c] : 0;
+    int incl = h;
+    for (int o = 1; o < 32; o <<= 1) {
+      const int t = __shfl_up_sync(0xffffffffu, incl, o);
+      if (lane >= o) incl += t;
+    }
+    if (lane == 31) warp_tot[w] = incl;
+    __syncthreads();
+    if (w == 0) {
+      int t = warp_tot[lane];
+      for (int o = 1; o < 32; o <<= 1) {
+        const int u = __shfl_up_sync(0xffffffffu, t, o);
+        if (lane >= o) t += u;
+      }
+      warp_tot[lane] = t;  // inclusive totals of the warps
+    }
+    __syncthreads();
+    const int excl = carry + (w ? warp_tot[w - 1] : 0) + incl - h;
+    if (c < K) {
+      base[c] = excl;
+      cursor[c] = excl;
+      if (h) counts[c] += static_cast<float>(h);
+      hist[c] = 0;
+    }
+    __syncthreads();
+    if (threadIdx.x == 0) carry += warp_tot[31];
+    __syncthreads();
+  }
+  if (threadIdx.x == 0) base[K] = carry;
+}
+
+__global__ void __launch_bounds__(256)
+kmeans_scatter_kernel(const int32_t* __restrict__ assign, int64_t n, int K, int* __restrict__ cursor,
+                      int32_t* __restrict__ perm) {
+  extern __shared__ int sh[];
+  int* cnt = sh;        // rows of this CTA's chunk per centre, then the fill counter
+  int* start = sh + K;  // first output slot reserved for (this CTA, centre)
+  for (int c = threadIdx.x; c < K; c += blockDim.x) cnt[c] = 0;
+  __syncthreads();
+  const int64_t chunk = (n + gridDim.x - 1) / gridDim.x;
+  const int64_t lo = chunk * blockIdx.x, hi = (lo + chunk < n) ? lo + chunk : n;
+  for (int64_t i = lo + threadIdx.x; i < hi; i += blockDim.x) {
+    const int a = assign[i];
+    if (a >= 0 && a < K) atomicAdd(&cnt[a], 1);
+  }
+  __syncthreads();
+  for (int c = threadIdx.x; c < K; c += blockDim.x) {
+    const int m = cnt[c];
+    if (m) start[c] = atomicAdd(&cursor[c], m);
+    cnt[c] = 0;
+  }
+  __syncthreads();
+  for (int64_t i = lo + threadIdx.x; i < hi; i += blockDim.x) {
+    const int a = assign[i];
+    if (a >= 0 && a < K) perm[start[a] + atomicAdd(&cnt[a], 1)] = static_cast<int32_t>(i);
+  }
+}
+
+constexpr int kSortedRun = 64;  // sorted rows per warp
+
+template <int D>
+__global__ void __launch_bounds__(256)
+kmeans_sorted_sum_kernel(const __nv_bfloat16* __restrict__ x, const int32_t* __restrict__ perm,
+                         const int* __restrict__ base, const float* __restrict__ dist, int K,
+                         float* __restrict__ sums, float* __restrict__ sse) {
+  static_assert(D == 64 || D == 128, "one uint2 (4 bf16) per lane");
+  const int lane = threadIdx.x & 31;
+  const bool active = lane * 4 < D;
+  const int total = base[K];
+  const int64_t warp = (static_cast<int64_t>(blockIdx.x) * blockDim.x + threadIdx.x) >> 5;
+  const int64_t nwarps = (static_cast<int64_t>(gridDim.x) * blockDim.x) >> 5;
+  float local_sse = 0.f;
+  for (int64_t run = warp; run * kSortedRun < total; run += nwarps) {
+    const int r0 = static_cast<int>(run * kSortedRun);
+    const int r1 = r0 + kSortedRun < total ? r0 + kSortedRun : total;
+    // centre of the first row: largest c with base[c] <= r0
+    int lo = 0, hi = K;
+    while (hi - lo > 1) {
+      const int mid = (lo + hi) >> 1;
+      if (base[mid] <= r0) lo = mid; else hi = mid;
+    }
+    int c = lo;
+    int next = base[c + 1];
+    float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
+    for (int b0 = r0; b0 < r1; b0 += 32) {
+      const int mine = b0 + lane < r1 ? perm[b0 + lane] : -1;
+      const float my_dist = mine >= 0 ? dist[mine] : 0.f;
+      const int cnt = r1 - b0 < 32 ? r1 - b0 : 32;
+      for (int r = 0; r < cnt; r += 4) {
+        uint2 raw[4];
+        int idx[4];
+#pragma unroll
+        for (int u = 0; u < 4; ++u) {
+          idx[u] = __shfl_sync(0xffffffffu, mine, (r + u) & 31);
+          raw[u] = make_uint2(0u, 0u);
+          if (r + u < cnt && active)
+            raw[u] = *reinterpret_cast<const uint2*>(x + static_cast<int64_t>(idx[u]) * D + lane * 4);
+        }
+#pragma unroll
+        for (int u = 0; u < 4; ++u) {
+          if (r + u >= cnt) break;
+          const int pos = b0 + r + u;
+          if (pos >= next) {  // uniform: the run crosses into another centre
+            if (active) red_gpu_v4(sums + static_cast<int64_t>(c) * D + lane * 4, acc);
+            acc = make_float4(0.f, 0.f, 0.f, 0.f);
+            do { ++c; next = base[c + 1]; } while (pos >= next);
+          }
+          const float2 p0 = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162*>(&raw[u].x));
+          const float2 p1 = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162*>(&raw[u].y));
+          acc.x += p0.x; acc.y += p0.y; acc.z += p1.x; acc.w += p1.y;
+          float xn = warp_sum(p0.x * p0.x + p0.y * p0.y + p1.x * p1.x + p1.y * p1.y);
+          const float d = __shfl_sync(0xffffffffu, my_dist, (r + u) & 31);
+          if (lane == 0) local_sse += fmaxf(xn + d, 0.f);
+        }
+      }
+    }
+    if (active) red_gpu_v4(sums + static_cast<int64_t>(c) * D + lane * 4, acc);
+  }
+  if (sse && lane == 0 && local_sse != 0.f) atomicAdd(sse, local_sse);
+}
+
 __global__ void __launch_bounds__(256)
 kmeans_delta_kernel(const float* __restrict__ centers, const float* __restrict__ counts_old,
                     const float* __restrict__ sums, const float* __restrict__ counts_batch, int K, int D, float alpha,
@@ -146,6 +300,40 @@ int mps_kmeans_accumulate(const void* x_bf16, const int32_t* assign, const float
   return 0;
 }
 
+int mps_kmeans_accumulate_sorted(const void* x_bf16, const int32_t* assign, const float* dist, int64_t n, int K,
+                                 int D, float* sums, float* counts, float* sse, int* sort_scratch, void* stream) {
+  if (n <= 0) return 0;
+  if ((D != 64 && D != 128) || K > 4096 || n > (int64_t(1) << 30) || !sort_scratch)
+    return mps_kmeans_accumulate(x_bf16, assign, dist, n, K, D, sums, counts, sse, stream);
+  auto st = static_cast<cudaStream_t>(stream);
+  int* hist = sort_scratch;          // [K]   zero on entry, left zero
+  int* base = hist + K;              // [K+1]
+  int* cursor = base + K + 1;        // [K]
+  int32_t* perm = cursor + K;        // [n]
+  static int sms = 0;
+  if (!sms) {
+    int dev = 0;
+    cudaGetDevice(&dev);
+    cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+  }
+  int64_t want = (n + 4095) / 4096;  // >= 16 rows per thread so the per-CTA histogram pays
+  const int grid = static_cast<int>(want < sms * 4 ? want : sms * 4);
+  mps::kmeans_hist_kernel<<<grid, 256, K * sizeof(int), st>>>(assign, n, K, hist);
+  mps::kmeans_scan_kernel<<<1, 1024, 0, st>>>(hist, K, base, cursor, counts);
+  mps::kmeans_scatter_kernel<<<grid, 256, 2 * K * sizeof(int), st>>>(assign, n, K, cursor, perm);
+  const int64_t runs = (n + mps::kSortedRun - 1) / mps::kSortedRun;
+  const int64_t ctas = (runs + 7) / 8;
+  const int g2 = static_cast<int>(ctas < sms * 8 ? ctas : sms * 8);
+  if (D == 128)
+    mps::kmeans_sorted_sum_kernel<128><<<g2, 256, 0, st>>>(static_cast<const __nv_bfloat16*>(x_bf16), perm, base, dist,
+                                                          K, sums, sse);
+  else
+    mps::kmeans_sorted_sum_kernel<64><<<g2, 256, 0, st>>>(static_cast<const __nv_bfloat16*>(x_bf16), perm, base, dist,
+                                                         K, sums, sse);
+  MPS_LAUNCH_CHECK();
+  return 0;
+}
+
 int mps_kmeans_delta(const float* centers, const float* counts_old, const float* sums, const float* counts_batch,
                      int K, int D, float alpha, float* delta_c, float* delta_n, void* stream) {
   const int64_t total = static_cast<int64_t>(K) * D;
@@ -176,11 +364,12 @@ int mps_kmeans_step(const MpsTableView* centers_view, const MpsClockView* center
                     const MpsTableView* counts_view, const MpsClockView* counts_clk, int worker, int progress,
                     int fold, const void* x_bf16, int64_t n, int K, int D, float alpha,
                     void* centers_bf16_scratch, float* cnorm_scratch, float* centers_f32, int* sync_ctr,
-                    int32_t* assign, float* dist, float* sums, float* counts_batch, float* sse, void* stream) {
+                    int32_t* assign, float* dist, float* sums, float* counts_batch, float* sse, int* sort_scratch,
+                    void* stream) {
   int rc = mps_kmeans_assign_tc(centers_view, centers_clk, progress, nullptr, x_bf16, n, K, D, centers_bf16_scratch,
                                 cnorm_scratch, centers_f32, sync_ctr, assign, dist, 0, stream);
   if (rc) return rc;
-  rc = mps_kmeans_accumulate(x_bf16, assign, dist, n, K, D, sums, counts_batch, sse, stream);
+  rc = mps_kmeans_accumulate_sorted(x_bf16, assign, dist, n, K, D, sums, counts_batch, sse, sort_scratch, stream);
   if (rc) return rc;
   rc = mps_kmeans_delta_push(centers_view, counts_view, counts_clk, progress, centers_f32, sums, counts_batch, K, D,
                              alpha, stream);

@@ -251,6 +251,14 @@ int mps_kmeans_assign_ref(const void* x_bf16, const void* centers_bf16, const fl
  * (kmeans_helper.hpp:236-266): sums [K*D] += x, counts [K] += 1, sse[0] += ||x - c||^2. */
 int mps_kmeans_accumulate(const void* x_bf16, const int32_t* assign, const float* dist, int64_t n,
                           int K, int D, float* sums, float* counts, float* sse, void* stream);
+/* The same accumulation without one atomic per point and lane: the batch's row indices are counting-
+ * sorted by centre (histogram, scan, scatter) and every warp sums a run of 64 sorted rows in registers,
+ * issuing atomics only where the centre changes.  sort_scratch: 3*K + 1 + n ints, its first K zero on
+ * entry (left zero).  D must be 64 or 128 and K <= 4096, otherwise (or with sort_scratch NULL) this is
+ * mps_kmeans_accumulate. */
+int mps_kmeans_accumulate_sorted(const void* x_bf16, const int32_t* assign, const float* dist, int64_t n,
+                                 int K, int D, float* sums, float* counts, float* sse, int* sort_scratch,
+                                 void* stream);
 /* Centroid normalisation: delta_c = alpha (sum - m c) / (n_old + m), delta_n = m. */
 int mps_kmeans_delta(const float* centers, const float* counts_old, const float* sums,
                      const float* counts_batch, int K, int D, float alpha, float* delta_c,
@@ -264,14 +272,14 @@ int mps_kmeans_delta_push(const MpsTableView* centers_view, const MpsTableView* 
                           const MpsClockView* counts_clk, int progress, const float* centers,
                           float* sums, float* counts_batch, int K, int D, float alpha, void* stream);
 /* One whole mini-batch iteration of a worker (kmeans.cpp:216-275) enqueued by a single host call:
- * assign (centre pull fused) -> accumulate -> delta + push of both tables -> Clock of both tables at
+ * assign (centre pull fused) -> accumulate (sorted, see above) -> delta + push of both tables -> Clock of both tables at
  * progress + 1 (fold: this worker is the last local one to clock, see mps_clock). */
 int mps_kmeans_step(const MpsTableView* centers_view, const MpsClockView* centers_clk,
                     const MpsTableView* counts_view, const MpsClockView* counts_clk, int worker,
                     int progress, int fold, const void* x_bf16, int64_t n, int K, int D, float alpha,
                     void* centers_bf16_scratch, float* cnorm_scratch, float* centers_f32, int* sync_ctr,
                     int32_t* assign, float* dist, float* sums, float* counts_batch, float* sse,
-                    void* stream);
+                    int* sort_scratch, void* stream);
 
 /* ---- dense logistic regression on tensor cores (csrc/kernels/dense_lr_tc.cu) ----------- */
 /* Forward of a dense batch (lr_example.cpp:293-305 for dense features): logits = X.w on

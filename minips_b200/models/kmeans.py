@@ -103,6 +103,7 @@ class KMeansTrainer:
         self.delta_n = torch.empty(K, dtype=torch.float32, device=self.dev)
         self.counts_old = torch.empty(K, dtype=torch.float32, device=self.dev)
         self._out = None
+        self._scratch = None
         self.allow_fused = True      # False forces the call-by-call path (tests, debugging)
 
     def step(self, start: int, batch: int, sse: Optional[torch.Tensor] = None) -> torch.Tensor:
@@ -123,10 +124,10 @@ class KMeansTrainer:
         self.sums.zero_()
         self.cnt.zero_()
         sp = self.tc._sp()
-        _lib.check(self.lib.mps_kmeans_accumulate(
+        _lib.check(self.lib.mps_kmeans_accumulate_sorted(
             C.c_void_p(xb.data_ptr()), C.c_void_p(assign.data_ptr()), C.c_void_p(dist.data_ptr()), n, self.K, self.D,
-            C.c_void_p(self.sums.data_ptr()), C.c_void_p(self.cnt.data_ptr()), C.c_void_p(sse.data_ptr()), sp),
-            "kmeans_accumulate")
+            C.c_void_p(self.sums.data_ptr()), C.c_void_p(self.cnt.data_ptr()), C.c_void_p(sse.data_ptr()),
+            C.c_void_p(self._sort_scratch(n).data_ptr()), sp), "kmeans_accumulate_sorted")
         _lib.check(self.lib.mps_kmeans_delta(
             C.c_void_p(self.assigner.c_f32.data_ptr()), C.c_void_p(self.counts_old.data_ptr()),
             C.c_void_p(self.sums.data_ptr()), C.c_void_p(self.cnt.data_ptr()), self.K, self.D, self.alpha,
@@ -137,6 +138,13 @@ class KMeansTrainer:
         self.tn.add_all(self.delta_n)
         self.tn.clock()
         return sse
+
+    def _sort_scratch(self, n: int) -> torch.Tensor:
+        """Counting-sort scratch of mps_kmeans_accumulate_sorted: hist [K] (zero), base [K+1], cursor [K], perm [n]."""
+        need = 3 * self.K + 1 + n
+        if self._scratch is None or self._scratch.numel() < need:
+            self._scratch = torch.zeros(need, dtype=torch.int32, device=self.dev)
+        return self._scratch
 
     def _fusable(self) -> bool:
         tc, tn = self.tc.table, self.tn.table
@@ -162,7 +170,7 @@ class KMeansTrainer:
                 C.c_void_p(a.c_bf16.data_ptr()), C.c_void_p(a.cnorm.data_ptr()), C.c_void_p(a.c_f32.data_ptr()),
                 C.c_void_p(a.sync.data_ptr()), C.c_void_p(assign.data_ptr()), C.c_void_p(dist.data_ptr()),
                 C.c_void_p(self.sums.data_ptr()), C.c_void_p(self.cnt.data_ptr()), C.c_void_p(sse.data_ptr()),
-                self.tc._sp()), "kmeans_step")
+                C.c_void_p(self._sort_scratch(n).data_ptr()), self.tc._sp()), "kmeans_step")
             ev = torch.cuda.Event()
             ev.record(s)
             for t, cl in ((tc, self.tc), (tn, self.tn)):

@@ -151,7 +151,8 @@ def _declare(lib):
         "mps_kmeans_delta": ([vp, vp, vp, vp, i32, i32, f32, vp, vp, vp], i32),
         "mps_kmeans_delta_push": ([P(TableView), P(TableView), P(ClockView), i32, vp, vp, vp, i32, i32, f32, vp], i32),
         "mps_kmeans_step": ([P(TableView), P(ClockView), P(TableView), P(ClockView), i32, i32, i32, vp, i64, i32, i32,
-                             f32, vp, vp, vp, vp, vp, vp, vp, vp, vp, vp], i32),
+                             f32, vp, vp, vp, vp, vp, vp, vp, vp, vp, vp, vp], i32),
+        "mps_kmeans_accumulate_sorted": ([vp, vp, vp, i64, i32, i32, vp, vp, vp, vp, vp], i32),
     }
     for name, (argtypes, restype) in sig.items():
         if hasattr(lib, name):

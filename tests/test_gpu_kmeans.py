@@ -132,3 +132,40 @@ def test_init_modes_cover_blobs():
             base = cost
         else:
             assert cost <= base * 1.05, (name, cost, base)  # D^2 seeding is no worse than random
+
+
+@pytest.mark.parametrize("D", [128, 64])
+def test_sorted_accumulate_matches_oracle(D):
+    """Counting-sort + run-sum accumulation against plain torch index_add (fp32) and the atomic kernel."""
+    import ctypes as C
+    from minips_b200.ops import _lib
+    lib = _lib.load()
+    K, n = 256, 100_003
+    g = torch.Generator(device="cuda").manual_seed(5)
+    x = torch.randn(n, D, device="cuda", generator=g).to(torch.bfloat16)
+    assign = torch.randint(0, K, (n,), device="cuda", generator=g, dtype=torch.int32)
+    assign[assign == 7] = 8            # an empty centre
+    assign[assign % 50 == 3] = 3       # a heavy one
+    dist = torch.randn(n, device="cuda", generator=g)
+    xf = x.float()
+    ref_sums = torch.zeros(K, D, device="cuda").index_add_(0, assign.long(), xf)
+    ref_cnt = torch.bincount(assign.long(), minlength=K).float()
+    ref_sse = ((xf * xf).sum(1) + dist).clamp_min(0).sum()
+    sp = _lib.stream_ptr()
+    scratch = torch.zeros(3 * K + 1 + n, dtype=torch.int32, device="cuda")
+    for rounds in (1, 2):              # twice: the scratch must come back reusable
+        sums = torch.zeros(K * D, device="cuda")
+        cnt = torch.zeros(K, device="cuda")
+        sse = torch.zeros(1, device="cuda")
+        _lib.check(lib.mps_kmeans_accumulate_sorted(
+            C.c_void_p(x.data_ptr()), C.c_void_p(assign.data_ptr()), C.c_void_p(dist.data_ptr()), n, K, D,
+            C.c_void_p(sums.data_ptr()), C.c_void_p(cnt.data_ptr()), C.c_void_p(sse.data_ptr()),
+            C.c_void_p(scratch.data_ptr()), sp), "accumulate_sorted")
+        torch.cuda.synchronize()
+        assert torch.equal(cnt, ref_cnt)
+        assert torch.allclose(sums.view(K, D), ref_sums, rtol=1e-4, atol=1e-2)
+        assert abs(sse.item() - ref_sse.item()) <= 1e-4 * abs(ref_sse.item())
+        assert int(scratch[:K].abs().sum()) == 0
+    perm = scratch[3 * K + 1:3 * K + 1 + n].long()
+    assert torch.equal(torch.sort(perm).values, torch.arange(n, device="cuda"))
+    assert bool((assign[perm][1:] >= assign[perm][:-1]).all())
