@@ -15,13 +15,18 @@
 
 namespace mps {
 
-__global__ void __launch_bounds__(256)
-clock_kernel(const __grid_constant__ MpsTableView v, const __grid_constant__ MpsClockView c,
-             int worker, int new_clock, int fold) {
+// With a single rank every reader of the pad and the shards is on this device: gpu-scope fences
+// are enough and cost a fraction of MEMBAR.SYS.
+__device__ __forceinline__ void fence_for(const MpsClockView& c) {
+  if (c.num_ranks > 1) fence_sys(); else __threadfence();
+}
+
+__device__ __forceinline__ void clock_body(const MpsTableView& v, const MpsClockView& c, int worker, int new_clock,
+                                           int fold, int bx, int nb) {
   // (1) signal.  Kernel boundary ordered this device's earlier pushes; the fence makes them
   //     visible system-wide before any replica can observe the new clock.
-  if (worker >= 0 && blockIdx.x == 0 && threadIdx.x == 0) {
-    fence_sys();
+  if (worker >= 0 && bx == 0 && threadIdx.x == 0) {
+    fence_for(c);
     for (int i = 0; i < c.num_ranks; ++i) {
       const int r = (c.my_rank + i) % c.num_ranks;
       st_relaxed_sys(c.pad[r] + MPS_PAD_PROGRESS + worker, new_clock);
@@ -36,8 +41,8 @@ clock_kernel(const __grid_constant__ MpsTableView v, const __grid_constant__ Mps
   if (!ok) return;
 
   // (3) fold my shards: weights += staging; staging = 0 (apply add_buffer_, bsp_model.cpp:20-23)
-  const int64_t tid = static_cast<int64_t>(blockIdx.x) * blockDim.x + threadIdx.x;
-  const int64_t stride = static_cast<int64_t>(gridDim.x) * blockDim.x;
+  const int64_t tid = static_cast<int64_t>(bx) * blockDim.x + threadIdx.x;
+  const int64_t stride = static_cast<int64_t>(nb) * blockDim.x;
   for (int s = c.own_first; s < c.own_first + c.own_count; ++s) {
     if (!v.staging[s]) continue;
     const int64_t len = static_cast<int64_t>(v.begin[s + 1] - v.begin[s]) * v.vals_per_key;
@@ -74,15 +79,34 @@ clock_kernel(const __grid_constant__ MpsTableView v, const __grid_constant__ Mps
   if (threadIdx.x == 0) {
     int* ctr = c.pad[c.my_rank] + MPS_PAD_LOCALCTR;
     const int done = atomicAdd(ctr, 1) + 1;
-    if (done == static_cast<int>(gridDim.x)) {
+    if (done == nb) {
       *ctr = 0;
-      fence_sys();
+      fence_for(c);
       for (int i = 0; i < c.num_ranks; ++i) {
         const int r = (c.my_rank + i) % c.num_ranks;
         for (int s = c.own_first; s < c.own_first + c.own_count; ++s)
           st_relaxed_sys(c.pad[r] + MPS_PAD_FOLDED + s, new_clock);
       }
     }
+  }
+}
+
+__global__ void __launch_bounds__(256)
+clock_kernel(const __grid_constant__ MpsTableView v, const __grid_constant__ MpsClockView c,
+             int worker, int new_clock, int fold) {
+  clock_body(v, c, worker, new_clock, fold, blockIdx.x, gridDim.x);
+}
+
+// Clock of two tables of one worker in a single launch (k-means: centres + counts): blockIdx.y picks
+// the table, nb0 / nb1 CTAs take part in each fold.
+__global__ void __launch_bounds__(256)
+clock2_kernel(const __grid_constant__ MpsTableView v0, const __grid_constant__ MpsClockView c0, int nb0,
+              const __grid_constant__ MpsTableView v1, const __grid_constant__ MpsClockView c1, int nb1,
+              int worker, int new_clock, int fold) {
+  if (blockIdx.y == 0) {
+    if (static_cast<int>(blockIdx.x) < nb0) clock_body(v0, c0, worker, new_clock, fold, blockIdx.x, nb0);
+  } else {
+    if (static_cast<int>(blockIdx.x) < nb1) clock_body(v1, c1, worker, new_clock, fold, blockIdx.x, nb1);
   }
 }
 
@@ -119,21 +143,36 @@ __global__ void reset_pad_kernel(const __grid_constant__ MpsClockView c, int sta
 
 extern "C" {
 
+static int clock_grid(const MpsTableView* view, const MpsClockView* clk, int fold) {
+  if (!(fold && clk->model == MPS_MODEL_BSP && clk->own_count > 0)) return 1;
+  int64_t len = 0;
+  for (int s = clk->own_first; s < clk->own_first + clk->own_count; ++s)
+    len += static_cast<int64_t>(view->begin[s + 1] - view->begin[s]) * view->vals_per_key;
+  static int sms = 0;
+  if (!sms) {
+    int dev = 0;
+    cudaGetDevice(&dev);
+    cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+  }
+  const int64_t want = (len / 4 + 256 * 4 - 1) / (256 * 4);
+  return static_cast<int>(want < 1 ? 1 : (want > sms * 4 ? sms * 4 : want));
+}
+
 int mps_clock(const MpsTableView* view, const MpsClockView* clk, int worker, int new_clock, int fold,
               void* stream) {
   auto st = static_cast<cudaStream_t>(stream);
-  int grid = 1;
-  if (fold && clk->model == MPS_MODEL_BSP && clk->own_count > 0) {
-    int64_t len = 0;
-    for (int s = clk->own_first; s < clk->own_first + clk->own_count; ++s)
-      len += static_cast<int64_t>(view->begin[s + 1] - view->begin[s]) * view->vals_per_key;
-    int dev = 0, sms = 148;
-    cudaGetDevice(&dev);
-    cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
-    int64_t want = (len / 4 + 256 * 4 - 1) / (256 * 4);
-    grid = static_cast<int>(want < 1 ? 1 : (want > sms * 4 ? sms * 4 : want));
-  }
+  const int grid = clock_grid(view, clk, fold);
   mps::clock_kernel<<<grid, 256, 0, st>>>(*view, *clk, worker, new_clock, fold);
+  MPS_LAUNCH_CHECK();
+  return 0;
+}
+
+int mps_clock2(const MpsTableView* view0, const MpsClockView* clk0, const MpsTableView* view1,
+               const MpsClockView* clk1, int worker, int new_clock, int fold, void* stream) {
+  auto st = static_cast<cudaStream_t>(stream);
+  const int g0 = clock_grid(view0, clk0, fold), g1 = clock_grid(view1, clk1, fold);
+  mps::clock2_kernel<<<dim3(g0 > g1 ? g0 : g1, 2), 256, 0, st>>>(*view0, *clk0, g0, *view1, *clk1, g1, worker,
+                                                                  new_clock, fold);
   MPS_LAUNCH_CHECK();
   return 0;
 }

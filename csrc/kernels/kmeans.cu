@@ -141,67 +141,96 @@ kmeans_scatter_kernel(const int32_t* __restrict__ assign, int64_t n, int K, int*
   }
 }
 
-constexpr int kSortedRun = 64;  // sorted rows per warp
+constexpr int kSortedRun = 64;  // sorted rows per unit
 
+// One "unit" = D/8 lanes (16 B = 8 bf16 per lane, so a unit covers one row per load); a warp holds
+// 32 / (D/8) independent units.  Every unit owns a run of kSortedRun sorted rows and keeps 8 row loads
+// in flight.  All loops have warp-uniform trip counts (rows past the end are predicated off) so the
+// shuffles stay convergent while units flush at different positions.
 template <int D>
 __global__ void __launch_bounds__(256)
 kmeans_sorted_sum_kernel(const __nv_bfloat16* __restrict__ x, const int32_t* __restrict__ perm,
                          const int* __restrict__ base, const float* __restrict__ dist, int K,
                          float* __restrict__ sums, float* __restrict__ sse) {
-  static_assert(D == 64 || D == 128, "one uint2 (4 bf16) per lane");
+  static_assert(D == 64 || D == 128, "8 bf16 per lane");
+  constexpr int LPR = D / 8;          // lanes per row
+  constexpr int UPW = 32 / LPR;       // units per warp
+  constexpr int U = 8;                // row loads in flight per unit
+  static_assert(LPR % U == 0, "a perm block is consumed in whole groups of U rows");
   const int lane = threadIdx.x & 31;
-  const bool active = lane * 4 < D;
+  const int sub = lane & (LPR - 1);   // lane within the unit
+  const int ubase = lane & ~(LPR - 1);
   const int total = base[K];
   const int64_t warp = (static_cast<int64_t>(blockIdx.x) * blockDim.x + threadIdx.x) >> 5;
   const int64_t nwarps = (static_cast<int64_t>(gridDim.x) * blockDim.x) >> 5;
   float local_sse = 0.f;
-  for (int64_t run = warp; run * kSortedRun < total; run += nwarps) {
-    const int r0 = static_cast<int>(run * kSortedRun);
+  for (int64_t w0 = warp; w0 * UPW * kSortedRun < total; w0 += nwarps) {
+    const int64_t unit = w0 * UPW + lane / LPR;
+    const int r0 = static_cast<int>(unit * kSortedRun < total ? unit * kSortedRun : total);
     const int r1 = r0 + kSortedRun < total ? r0 + kSortedRun : total;
-    // centre of the first row: largest c with base[c] <= r0
-    int lo = 0, hi = K;
-    while (hi - lo > 1) {
-      const int mid = (lo + hi) >> 1;
-      if (base[mid] <= r0) lo = mid; else hi = mid;
+    int c = 0, next = 0x7fffffff;
+    if (r0 < r1) {  // centre of the first row: largest c with base[c] <= r0
+      int lo = 0, hi = K;
+      while (hi - lo > 1) {
+        const int mid = (lo + hi) >> 1;
+        if (base[mid] <= r0) lo = mid; else hi = mid;
+      }
+      c = lo;
+      next = base[c + 1];
     }
-    int c = lo;
-    int next = base[c + 1];
-    float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
-    for (int b0 = r0; b0 < r1; b0 += 32) {
-      const int mine = b0 + lane < r1 ? perm[b0 + lane] : -1;
-      const float my_dist = mine >= 0 ? dist[mine] : 0.f;
-      const int cnt = r1 - b0 < 32 ? r1 - b0 : 32;
-      for (int r = 0; r < cnt; r += 4) {
-        uint2 raw[4];
-        int idx[4];
+    float acc[8];
 #pragma unroll
-        for (int u = 0; u < 4; ++u) {
-          idx[u] = __shfl_sync(0xffffffffu, mine, (r + u) & 31);
-          raw[u] = make_uint2(0u, 0u);
-          if (r + u < cnt && active)
-            raw[u] = *reinterpret_cast<const uint2*>(x + static_cast<int64_t>(idx[u]) * D + lane * 4);
+    for (int e = 0; e < 8; ++e) acc[e] = 0.f;
+    for (int b0 = 0; b0 < kSortedRun; b0 += LPR) {
+      const int pl = r0 + b0 + sub;
+      const int mine = pl < r1 ? perm[pl] : -1;
+      const float my_dist = mine >= 0 ? dist[mine] : 0.f;
+#pragma unroll
+      for (int j0 = 0; j0 < LPR; j0 += U) {
+        uint4 raw[U];
+        int idx[U];
+#pragma unroll
+        for (int u = 0; u < U; ++u) {
+          idx[u] = __shfl_sync(0xffffffffu, mine, ubase + j0 + u);
+          raw[u] = make_uint4(0u, 0u, 0u, 0u);
+          if (idx[u] >= 0) raw[u] = *reinterpret_cast<const uint4*>(x + static_cast<int64_t>(idx[u]) * D + sub * 8);
         }
 #pragma unroll
-        for (int u = 0; u < 4; ++u) {
-          if (r + u >= cnt) break;
-          const int pos = b0 + r + u;
-          if (pos >= next) {  // uniform: the run crosses into another centre
-            if (active) red_gpu_v4(sums + static_cast<int64_t>(c) * D + lane * 4, acc);
-            acc = make_float4(0.f, 0.f, 0.f, 0.f);
-            do { ++c; next = base[c + 1]; } while (pos >= next);
-          }
+        for (int u = 0; u < U; ++u) {
+          const int pos = r0 + b0 + j0 + u;
           const float2 p0 = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162*>(&raw[u].x));
           const float2 p1 = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162*>(&raw[u].y));
-          acc.x += p0.x; acc.y += p0.y; acc.z += p1.x; acc.w += p1.y;
-          float xn = warp_sum(p0.x * p0.x + p0.y * p0.y + p1.x * p1.x + p1.y * p1.y);
-          const float d = __shfl_sync(0xffffffffu, my_dist, (r + u) & 31);
-          if (lane == 0) local_sse += fmaxf(xn + d, 0.f);
+          const float2 p2 = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162*>(&raw[u].z));
+          const float2 p3 = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162*>(&raw[u].w));
+          if (idx[u] >= 0 && pos >= next) {  // this unit's run crosses into another centre
+            float* dst = sums + static_cast<int64_t>(c) * D + sub * 8;
+            red_gpu_v4(dst, make_float4(acc[0], acc[1], acc[2], acc[3]));
+            red_gpu_v4(dst + 4, make_float4(acc[4], acc[5], acc[6], acc[7]));
+#pragma unroll
+            for (int e = 0; e < 8; ++e) acc[e] = 0.f;
+            do { ++c; next = base[c + 1]; } while (pos >= next);
+          }
+          acc[0] += p0.x; acc[1] += p0.y; acc[2] += p1.x; acc[3] += p1.y;
+          acc[4] += p2.x; acc[5] += p2.y; acc[6] += p3.x; acc[7] += p3.y;
+          float xn = p0.x * p0.x + p0.y * p0.y + p1.x * p1.x + p1.y * p1.y + p2.x * p2.x + p2.y * p2.y +
+                     p3.x * p3.x + p3.y * p3.y;
+#pragma unroll
+          for (int o = LPR / 2; o > 0; o >>= 1) xn += __shfl_xor_sync(0xffffffffu, xn, o);
+          const float d = __shfl_sync(0xffffffffu, my_dist, ubase + j0 + u);
+          if (sub == 0 && idx[u] >= 0) local_sse += fmaxf(xn + d, 0.f);
         }
       }
     }
-    if (active) red_gpu_v4(sums + static_cast<int64_t>(c) * D + lane * 4, acc);
+    if (r0 < r1) {
+      float* dst = sums + static_cast<int64_t>(c) * D + sub * 8;
+      red_gpu_v4(dst, make_float4(acc[0], acc[1], acc[2], acc[3]));
+      red_gpu_v4(dst + 4, make_float4(acc[4], acc[5], acc[6], acc[7]));
+    }
   }
-  if (sse && lane == 0 && local_sse != 0.f) atomicAdd(sse, local_sse);
+  if (sse) {
+    local_sse = warp_sum(local_sse);
+    if (lane == 0 && local_sse != 0.f) atomicAdd(sse, local_sse);
+  }
 }
 
 __global__ void __launch_bounds__(256)
@@ -322,7 +351,8 @@ int mps_kmeans_accumulate_sorted(const void* x_bf16, const int32_t* assign, cons
   mps::kmeans_scan_kernel<<<1, 1024, 0, st>>>(hist, K, base, cursor, counts);
   mps::kmeans_scatter_kernel<<<grid, 256, 2 * K * sizeof(int), st>>>(assign, n, K, cursor, perm);
   const int64_t runs = (n + mps::kSortedRun - 1) / mps::kSortedRun;
-  const int64_t ctas = (runs + 7) / 8;
+  const int upw = 32 / (D / 8);                       // units per warp
+  const int64_t ctas = (runs + 8 * upw - 1) / (8 * upw);
   const int g2 = static_cast<int>(ctas < sms * 8 ? ctas : sms * 8);
   if (D == 128)
     mps::kmeans_sorted_sum_kernel<128><<<g2, 256, 0, st>>>(static_cast<const __nv_bfloat16*>(x_bf16), perm, base, dist,
@@ -374,9 +404,7 @@ int mps_kmeans_step(const MpsTableView* centers_view, const MpsClockView* center
   rc = mps_kmeans_delta_push(centers_view, counts_view, counts_clk, progress, centers_f32, sums, counts_batch, K, D,
                              alpha, stream);
   if (rc) return rc;
-  rc = mps_clock(centers_view, centers_clk, worker, progress + 1, fold, stream);
-  if (rc) return rc;
-  return mps_clock(counts_view, counts_clk, worker, progress + 1, fold, stream);
+  return mps_clock2(centers_view, centers_clk, counts_view, counts_clk, worker, progress + 1, fold, stream);
 }
 
 }  // extern "C"

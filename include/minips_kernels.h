@@ -112,6 +112,9 @@ int mps_push_dense(const MpsTableView* view, void* src, int zero_src, int rot_sh
  * the weights of its shards and publishes folded[s] = new_clock (bsp_model.cpp:14-32). */
 int mps_clock(const MpsTableView* view, const MpsClockView* clk, int worker, int new_clock,
               int fold, void* stream);
+/* Clock of two tables of the same worker in one launch (k-means: centres and counts). */
+int mps_clock2(const MpsTableView* view0, const MpsClockView* clk0, const MpsTableView* view1,
+               const MpsClockView* clk1, int worker, int new_clock, int fold, void* stream);
 /* Device-side barrier over the pads (comm/mailbox.cpp:362-396 semantics). */
 int mps_barrier(const MpsClockView* clk, int epoch, void* stream);
 /* ResetWorker (bsp_model.cpp:70-83): zero progress/folded on the LOCAL pad. */

@@ -42,8 +42,8 @@ def run(args, emit):
         tc.clock()
         tn.clock()
         tr = KMeansTrainer(tc, tn, x, K, alpha=1.0)
-        # fused: assign(+pull) / hist / scan / scatter / run-sum / delta+push / clock x2 from one host call
-        res["launches_per_step"] = 8 if tr._fusable() else 13
+        # fused: assign(+pull) / hist / scan / scatter / run-sum / delta+push / clock of both tables, from one host call
+        res["launches_per_step"] = 7 if tr._fusable() else 13
         starts = torch.randint(0, max(1, n_local - B), (warm + steps,), generator=g).tolist()
         sse = torch.zeros(1, device=dev)
         for s in starts[:warm]:
