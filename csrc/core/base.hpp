@@ -311,10 +311,10 @@ template <typename T>
 class ThreadsafeQueue {
  public:
   void Push(T v) {
-    {
-      std::lock_guard<std::mutex> lk(mu_);
-      q_.push_back(std::move(v));
-    }
+    // notify under the lock: a consumer that owns the queue (Engine::InitTable keeps one on its stack) may
+    // destroy it as soon as it has popped, which it cannot do before this thread lets go of the mutex
+    std::lock_guard<std::mutex> lk(mu_);
+    q_.push_back(std::move(v));
     cv_.notify_all();
   }
   void WaitAndPop(T* out) {

@@ -283,16 +283,19 @@ void Mailbox::Dispatch(Message& msg) {
     case Flag::kForceQuit: {
       const uint32_t gone = static_cast<uint32_t>(msg.meta.sender);
       bool removed = false;
-      for (auto it = nodes_.begin(); it != nodes_.end(); ++it)
-        if (it->id == gone) {
-          nodes_.erase(it);
-          removed = true;
-          break;
-        }
+      {
+        // nodes_ is read by Barrier() on user threads: it changes only under barrier_mu_
+        std::lock_guard<std::mutex> lk(barrier_mu_);
+        for (auto it = nodes_.begin(); it != nodes_.end(); ++it)
+          if (it->id == gone) {
+            nodes_.erase(it);
+            removed = true;
+            break;
+          }
+        if (removed) barrier_cv_.notify_all();  // the barrier target just shrank
+      }
       if (removed) {
         if (listener_) listener_->OnForceQuit(gone);
-        std::lock_guard<std::mutex> lk(barrier_mu_);
-        barrier_cv_.notify_all();  // the barrier target just shrank
       }
       return;
     }
@@ -370,7 +373,11 @@ void Mailbox::Barrier() {
   Message m;
   m.meta.flag = Flag::kBarrier;
   m.meta.sender = static_cast<int>(node_.id);
-  const std::vector<Node> peers = nodes_;
+  std::vector<Node> peers;
+  {
+    std::lock_guard<std::mutex> lk(barrier_mu_);
+    peers = nodes_;
+  }
   for (const auto& n : peers) {
     m.meta.recver = static_cast<int>(n.id);
     SendTo(n.id, m);
@@ -386,14 +393,22 @@ void Mailbox::ForceQuit(uint32_t node_id) {
   Message m;
   m.meta.flag = Flag::kForceQuit;
   m.meta.sender = static_cast<int>(node_id);
-  const std::vector<Node> peers = nodes_;
+  std::vector<Node> peers;
+  {
+    std::lock_guard<std::mutex> lk(barrier_mu_);
+    peers = nodes_;
+  }
   for (const auto& n : peers) {
     m.meta.recver = static_cast<int>(n.id);
     SendTo(n.id, m);
   }
 }
 
-void Mailbox::UpdateNodes(const std::vector<Node>& nodes) { nodes_ = nodes; }
+void Mailbox::UpdateNodes(const std::vector<Node>& nodes) {
+  std::lock_guard<std::mutex> lk(barrier_mu_);
+  nodes_ = nodes;
+  barrier_cv_.notify_all();
+}
 
 // ------------------------------------------------------------------ Sender
 void Sender::Start() {

@@ -125,6 +125,17 @@ __global__ void barrier_kernel(const __grid_constant__ MpsClockView c, int epoch
   });
 }
 
+// Device-side straggler injection (the reference sleeps the worker thread, lr_example.cpp:347-353): hold
+// the worker's stream for `ns` nanoseconds so that its clock really lags on the device timeline.
+__global__ void straggle_kernel(long long ns) {
+  unsigned long long t0, t;
+  asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t0));
+  do {
+    __nanosleep(1000);
+    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+  } while (static_cast<long long>(t - t0) < ns);
+}
+
 __global__ void reset_pad_kernel(const __grid_constant__ MpsClockView c, int start_clock) {
   int* pad = c.pad[c.my_rank];
   for (int i = threadIdx.x; i < MPS_MAX_WORKERS; i += blockDim.x) {
@@ -179,6 +190,13 @@ int mps_clock2(const MpsTableView* view0, const MpsClockView* clk0, const MpsTab
 
 int mps_barrier(const MpsClockView* clk, int epoch, void* stream) {
   mps::barrier_kernel<<<1, 32, 0, static_cast<cudaStream_t>(stream)>>>(*clk, epoch);
+  MPS_LAUNCH_CHECK();
+  return 0;
+}
+
+int mps_straggle(long long ns, void* stream) {
+  if (ns <= 0) return 0;
+  mps::straggle_kernel<<<1, 1, 0, static_cast<cudaStream_t>(stream)>>>(ns);
   MPS_LAUNCH_CHECK();
   return 0;
 }

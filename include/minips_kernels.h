@@ -117,6 +117,9 @@ int mps_clock2(const MpsTableView* view0, const MpsClockView* clk0, const MpsTab
                const MpsClockView* clk1, int worker, int new_clock, int fold, void* stream);
 /* Device-side barrier over the pads (comm/mailbox.cpp:362-396 semantics). */
 int mps_barrier(const MpsClockView* clk, int epoch, void* stream);
+/* Injected straggler (lr_example.cpp:347-353 sleeps the worker thread): stalls `stream` for ns
+ * nanoseconds on the device, so the worker's next Clock is late for every peer. */
+int mps_straggle(long long ns, void* stream);
 /* ResetWorker (bsp_model.cpp:70-83): zero progress/folded on the LOCAL pad. */
 int mps_reset_pad(const MpsClockView* clk, int start_clock, void* stream);
 

@@ -107,7 +107,9 @@ def main(argv=None):
                 with open(f"{rep_prefix}_{rank}", "a") as f:
                     f.write(f"{i}\t{(time.time() - t0) * 1e3:.3f}\n")
             if p_straggle > 0 and random.random() < p_straggle:
-                time.sleep(random.random() * 0.1)  # lr_example.cpp:347-353
+                # lr_example.cpp:347-353 sleeps the worker thread; here the worker's STREAM is held, so its
+                # next clock is late on the device timeline and peers meet the consistency gate for real
+                client.straggle(random.random() * 0.1)
         torch.cuda.synchronize()
         elapsed = (time.time() - t0) * 1e3
         loss, acc = tr.evaluate()

@@ -18,6 +18,7 @@ import torch
 from ..ops import _lib
 from ..parallel.device_table import KVClientTable
 from ..parallel.types import ModelType
+from ..utils.tracing import traced
 
 
 def make_blobs(n: int, d: int, k_true: int, device="cuda", seed: int = 0, spread: float = 0.15,
@@ -106,6 +107,7 @@ class KMeansTrainer:
         self._scratch = None
         self.allow_fused = True      # False forces the call-by-call path (tests, debugging)
 
+    @traced("kmeans.step")
     def step(self, start: int, batch: int, sse: Optional[torch.Tensor] = None) -> torch.Tensor:
         """One iteration on rows [start, start+batch).  Returns the 1-element SSE tensor."""
         xb = self.x[start:start + batch]

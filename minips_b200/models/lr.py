@@ -15,6 +15,7 @@ import torch
 from ..ops import _lib
 from ..parallel.device_table import DeviceTable, KVClientTable
 from ..parallel.types import ModelType
+from ..utils.tracing import traced
 
 
 @dataclass
@@ -110,6 +111,7 @@ class SparseLRTrainer:
         nnz_per_row = max(1, self.data.nnz // max(1, self.data.n_rows))
         return batch * nnz_per_row * 4 >= self.table.num_keys
 
+    @traced("lr.train_dense")
     def train_dense(self, batch_starts: torch.Tensor, batch: int, max_ctas: int = 0,
                     csr: Optional[_lib.Csr] = None, loss: Optional[torch.Tensor] = None,
                     timeline: Optional[torch.Tensor] = None) -> torch.Tensor:
@@ -142,6 +144,7 @@ class SparseLRTrainer:
             t.lock.notify_all()
         return loss
 
+    @traced("lr.train_stream")
     def train_stream(self, loader, row_starts, host_loss: Optional[torch.Tensor] = None) -> torch.Tensor:
         """End-to-end iterations: every step copies its batch from pinned host memory (double
         buffered on a copy stream), trains on it, and returns its (logloss, #correct) to a
@@ -164,6 +167,7 @@ class SparseLRTrainer:
             host_loss[i].copy_(dev_loss[i], non_blocking=True)
         return host_loss
 
+    @traced("lr.step_sparse")
     def step_sparse(self, row_begin: int, batch: int, loss: Optional[torch.Tensor] = None) -> torch.Tensor:
         """One iteration in the sparse regime: fused pull+forward+grad+push kernel, then Clock."""
         c = self.client

@@ -127,6 +127,7 @@ def _declare(lib):
         "mps_clock": ([P(TableView), P(ClockView), i32, i32, i32, vp], i32),
         "mps_barrier": ([P(ClockView), i32, vp], i32),
         "mps_reset_pad": ([P(ClockView), i32, vp], i32),
+        "mps_straggle": ([C.c_longlong, vp], i32),
         "mps_lr_step_sparse": ([P(TableView), P(ClockView), i32, i32, P(Csr), i64, i64, f32, vp, vp], i32),
         "mps_lr_train_dense": ([P(TableView), P(ClockView), i32, i32, P(Csr), vp, i32, i64, f32, vp, vp, vp,
                                 i32, vp], i32),

@@ -342,6 +342,10 @@ class KVClientTable:
             t.lock.notify_all()
         self.progress = new_clock
 
+    def straggle(self, seconds: float):
+        """Injected straggler: stall this worker's stream for `seconds` on the device."""
+        _lib.check(self.lib.mps_straggle(int(seconds * 1e9), self._sp()), "straggle")
+
     def checkpoint(self):
         """Blocking dump of every shard + tracker state (kv_client_table.hpp:136-154)."""
         if self.engine is None:

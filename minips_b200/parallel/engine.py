@@ -18,6 +18,7 @@ import torch
 
 from .device_table import DeviceTable, KVClientTable
 from .heap import _ControlPlane
+from ..utils.tracing import traced
 from .types import (MLTask, ModelType, Node, Range, SimpleIdMapper, StorageType, WorkerAlloc, WorkerSpec,
                     even_ranges)
 
@@ -122,6 +123,7 @@ class Engine:
 
     CreateTable = create_table
 
+    @traced("engine.barrier")
     def barrier(self):
         """Process barrier (reference Mailbox::Barrier via Engine::Barrier, engine.cpp:186-188)."""
         if torch.cuda.is_available():
@@ -130,6 +132,7 @@ class Engine:
 
     Barrier = barrier
 
+    @traced("engine.device_barrier")
     def device_barrier(self, table_id: int, stream=None):
         """Barrier among the ranks ON THE DEVICE (flags in the table's signal pad, no host round
         trip): every rank's `stream` continues only after every rank enqueued its barrier.
@@ -149,6 +152,7 @@ class Engine:
                 spec.insert_worker_id_thread_id(w, self.id_mapper.allocate_worker_thread(a.node_id))
         return spec
 
+    @traced("engine.run")
     def run(self, task: MLTask):
         assert task.is_setup(), "task needs lambda, worker_alloc and tables"
         spec = self.allocate_workers(task.get_worker_alloc())
@@ -246,6 +250,7 @@ class Engine:
         if self.dump_callback:
             self.dump_callback()
 
+    @traced("engine.checkpoint_table")
     def checkpoint_table(self, table_id: int, client: Optional[KVClientTable] = None):
         """KVClientTable::CheckPoint (kv_client_table.hpp:136-154).  Collective on this backend."""
         from ..utils import checkpoint as ckpt

@@ -165,6 +165,39 @@ def main():
     assert abs(cost_dev - cost_ref) <= 2e-2 * cost_ref + 1e-3, (rank, cost_dev, cost_ref)
     assert (out7["n"] - n_ref).abs().sum().item() <= 0.05 * world * it7 * b7
 
+    # ---- 8. injected device-side straggler: under SSP(1) the fast ranks are held back by rank 0's late clocks,
+    #         under ASP they are not
+    t8s = engine.create_table(num_dims=4096, model_type=ModelType.SSP, staleness=1)
+    t8a = engine.create_table(num_dims=4096, model_type=ModelType.ASP)
+    k8 = torch.arange(0, 4096, 7)
+    took = {}
+
+    def straggle_fn(tid, name):
+        def fn(info):
+            t = info.create_kv_client_table(tid)
+            torch.cuda.synchronize()
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0.record()
+            for _ in range(10):
+                t.get(k8)
+                if rank == 0:
+                    t.straggle(0.003)
+                t.add(k8, torch.ones(k8.numel()))
+                t.clock()
+            t.get(k8)
+            e1.record()
+            torch.cuda.synchronize()
+            took[name] = e0.elapsed_time(e1)
+        return fn
+
+    run_task(engine, [t8s], straggle_fn(t8s, "ssp"))
+    run_task(engine, [t8a], straggle_fn(t8a, "asp"))
+    if rank == 0:
+        assert took["ssp"] >= 29.0 and took["asp"] >= 29.0, took
+    else:
+        assert took["ssp"] >= 8 * 3.0 - 1.0, (rank, took)      # may run at most staleness + 1 clocks ahead
+        assert took["asp"] < took["ssp"] / 2, (rank, took)
+
     engine.stop_everything()
     import torch.distributed as dist
     if dist.is_initialized():

@@ -75,3 +75,18 @@ def test_even_ranges_last_takes_remainder():
     # Engine::getRanges, driver/engine.hpp:158-172
     assert even_ranges(10, 3) == [(0, 3), (3, 6), (6, 10)]
     assert even_ranges(8, 8)[-1] == (7, 8)
+
+
+def test_tracing_helpers_are_noops_without_cuda_or_flag():
+    from minips_b200.utils.tracing import PhaseTimer, nvtx_range, traced
+
+    @traced("x")
+    def f(a):
+        return a + 1
+
+    with nvtx_range("outer"):
+        assert f(1) == 2
+    pt = PhaseTimer(enabled=False)
+    with pt.phase("p"):
+        pass
+    assert pt.summary() == {}
