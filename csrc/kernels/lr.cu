@@ -141,8 +141,8 @@ __device__ __forceinline__ int64_t flat_begin1(const MpsTableView& v, int s) {
 }
 
 // slab-pull all shards into replica[0 .. num_dims)
-__device__ __forceinline__ void slab_pull(const MpsTableView& v, int rot_shard, float* __restrict__ replica,
-                                          int64_t tid, int64_t nthreads) {
+__device__ __forceinline__ void slab_pull_by_shard(const MpsTableView& v, int rot_shard, float* __restrict__ replica,
+                                                   int64_t tid, int64_t nthreads) {
   const int S = v.num_shards;
   for (int i = 0; i < S; ++i) {
     int s = rot_shard + i;
@@ -165,8 +165,8 @@ __device__ __forceinline__ void slab_pull(const MpsTableView& v, int rot_shard, 
 // slab-push gacc into the owners' WEIGHTS (vector reds), clearing gacc behind itself.  The
 // fused kernel adds in place even under BSP: isolation comes from the "pulled" flags (every
 // worker finished its Get of this clock before anyone adds), so no staging pass is needed.
-__device__ __forceinline__ void slab_push(const MpsTableView& v, int rot_shard, float* __restrict__ gacc,
-                                          int64_t tid, int64_t nthreads) {
+__device__ __forceinline__ void slab_push_by_shard(const MpsTableView& v, int rot_shard, float* __restrict__ gacc,
+                                                   int64_t tid, int64_t nthreads) {
   const int S = v.num_shards;
   for (int i = 0; i < S; ++i) {
     int s = rot_shard + i;
@@ -194,6 +194,69 @@ __device__ __forceinline__ void slab_push(const MpsTableView& v, int rot_shard, 
         if (x != 0.f) { red_sys(dst + q, x); src[q] = 0.f; }
       }
     }
+  }
+}
+
+// Flat versions.  The per-shard loops above hand every shard to the SAME low-numbered threads, which
+// then pay one peer round trip per shard, one after the other (8 shards = 8 NVLink latencies while most
+// of the grid idles).  Here the whole key range is one index space: every thread owns one or two 16-byte
+// chunks, routes each to its owner and has all its loads in flight at once.  Needs every shard boundary
+// on a multiple of 4 values; otherwise the per-shard loops run.
+__device__ __forceinline__ bool shards_aligned4(const MpsTableView& v) {
+  bool ok = true;
+  for (int s = 1; s < v.num_shards; ++s) ok = ok && ((flat_begin1(v, s) & 3) == 0);
+  return ok;
+}
+
+__device__ __forceinline__ const float* chunk_src(const MpsTableView& v, int64_t f) {
+  const int s = owner_of(v, v.begin[0] + static_cast<uint32_t>(f));
+  return static_cast<const float*>(v.weights[s]) + (f - flat_begin1(v, s));
+}
+
+__device__ __forceinline__ void slab_pull(const MpsTableView& v, int rot_shard, float* __restrict__ replica,
+                                          int64_t tid, int64_t nthreads) {
+  if (!shards_aligned4(v)) {
+    slab_pull_by_shard(v, rot_shard, replica, tid, nthreads);
+    return;
+  }
+  const int64_t total = flat_begin1(v, v.num_shards);
+  const int64_t total4 = total >> 2;
+  const int64_t rot4 = flat_begin1(v, rot_shard) >> 2;  // start with the local shard, peers follow
+  for (int64_t q = tid; q < total4; q += 2 * nthreads) {
+    int64_t g0 = q + rot4, g1 = q + nthreads + rot4;
+    if (g0 >= total4) g0 -= total4;
+    const bool two = q + nthreads < total4;
+    if (g1 >= total4) g1 -= total4;
+    const float4 a = ld_sys_v4(chunk_src(v, g0 << 2));
+    float4 b = make_float4(0.f, 0.f, 0.f, 0.f);
+    if (two) b = ld_sys_v4(chunk_src(v, g1 << 2));
+    *reinterpret_cast<float4*>(replica + (g0 << 2)) = a;
+    if (two) *reinterpret_cast<float4*>(replica + (g1 << 2)) = b;
+  }
+  for (int64_t f = (total4 << 2) + tid; f < total; f += nthreads) replica[f] = ld_sys(chunk_src(v, f));
+}
+
+__device__ __forceinline__ void slab_push(const MpsTableView& v, int rot_shard, float* __restrict__ gacc,
+                                          int64_t tid, int64_t nthreads) {
+  if (!shards_aligned4(v)) {
+    slab_push_by_shard(v, rot_shard, gacc, tid, nthreads);
+    return;
+  }
+  const int64_t total = flat_begin1(v, v.num_shards);
+  const int64_t total4 = total >> 2;
+  const int64_t rot4 = flat_begin1(v, rot_shard) >> 2;
+  for (int64_t q = tid; q < total4; q += nthreads) {
+    int64_t g = q + rot4;
+    if (g >= total4) g -= total4;
+    const float4 x = ld_cg_v4(gacc + (g << 2));
+    if (x.x != 0.f || x.y != 0.f || x.z != 0.f || x.w != 0.f) {
+      red_sys_v4(const_cast<float*>(chunk_src(v, g << 2)), x);
+      *reinterpret_cast<float4*>(gacc + (g << 2)) = make_float4(0.f, 0.f, 0.f, 0.f);
+    }
+  }
+  for (int64_t f = (total4 << 2) + tid; f < total; f += nthreads) {
+    const float x = ld_cg(gacc + f);
+    if (x != 0.f) { red_sys(const_cast<float*>(chunk_src(v, f)), x); gacc[f] = 0.f; }
   }
 }
 
