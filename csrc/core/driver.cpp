@@ -132,9 +132,9 @@ void Engine::StartEverything(int num_server_threads_per_node) {
 }
 
 void Engine::StopEverything() {
-  StopHeartbeatThread();
-  StopMailbox();  // barrier, stop receiver, kExit into every registered queue (servers, helper)
-  StopSender();
+  StopHeartbeatThread();  // queues the goodbye heartbeat on the sender
+  StopSender();           // drains the sender queue (the goodbye must leave before the sockets close; engine.hpp:174-180)
+  StopMailbox();          // barrier, stop receiver, kExit into every registered queue (servers, helper)
   StopServerThreads();
   StopWorkerThreads();
 }
