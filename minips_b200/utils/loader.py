@@ -14,9 +14,38 @@ import torch
 from ..models.lr import CsrBatchSource
 
 
+class PackedCsrHost:
+    """Compact pinned-host form of a CSR data set for the H2D stream: row lengths as u8, feature ids as
+    24-bit little-endian integers, labels as u8, values unchanged (fp32).  Lossless when every row has
+    < 256 non-zeros, every feature id is < 2^24 and labels are 0/1; `from_csr` returns None otherwise."""
+
+    def __init__(self, row_ptr, row_len, col24, val, label_u8):
+        self.row_ptr, self.row_len, self.col24, self.val, self.label_u8 = row_ptr, row_len, col24, val, label_u8
+        self.n_rows = row_len.numel()
+        self.nnz = val.numel()
+
+    @staticmethod
+    def from_csr(host: CsrBatchSource) -> "Optional[PackedCsrHost]":
+        rp = host.row_ptr.cpu()
+        lens = rp[1:] - rp[:-1]
+        col = host.col.cpu()
+        lab = host.label.cpu()
+        if int(lens.max()) > 255 or int(col.max()) >= (1 << 24) or int(col.min()) < 0:
+            return None
+        if not bool(((lab == 0) | (lab == 1)).all()):
+            return None
+        col24 = col.to(torch.int32).contiguous().view(torch.uint8).view(-1, 4)[:, :3].contiguous().view(-1)
+        return PackedCsrHost(rp.contiguous(), lens.to(torch.uint8).pin_memory(), col24.pin_memory(),
+                             host.val.cpu().contiguous().pin_memory(), lab.to(torch.uint8).pin_memory())
+
+
 class AsyncBatchLoader:
-    def __init__(self, host: CsrBatchSource, batch: int, device, depth: int = 2):
-        assert host.row_ptr.is_pinned() and host.col.is_pinned() and host.val.is_pinned() and host.label.is_pinned()
+    def __init__(self, host, batch: int, device, depth: int = 2):
+        self.packed = isinstance(host, PackedCsrHost)
+        if self.packed:
+            assert host.row_len.is_pinned() and host.col24.is_pinned() and host.val.is_pinned() and host.label_u8.is_pinned()
+        else:
+            assert host.row_ptr.is_pinned() and host.col.is_pinned() and host.val.is_pinned() and host.label.is_pinned()
         self.host = host
         self.batch = batch
         self.device = device
@@ -35,6 +64,13 @@ class AsyncBatchLoader:
                 "ready": torch.cuda.Event(),
                 "free": None,
             })
+            if self.packed:
+                self.slots[-1].update({
+                    "row_len": torch.empty(batch, dtype=torch.uint8, device=device),
+                    "col24": torch.empty(3 * max_nnz + 16, dtype=torch.uint8, device=device),
+                    "label_u8": torch.empty(batch, dtype=torch.uint8, device=device),
+                    "scratch": torch.empty(batch // 4096 + 4, dtype=torch.int32, device=device),
+                })
         self.bytes_per_batch = 0
         self._i = 0
 
@@ -49,14 +85,20 @@ class AsyncBatchLoader:
         with torch.cuda.stream(self.copy_stream):
             if slot["free"] is not None:
                 self.copy_stream.wait_event(slot["free"])
-            slot["row_ptr"].copy_(h.row_ptr[row_start:row_start + B + 1], non_blocking=True)
-            slot["col"][:e - b].copy_(h.col[b:e], non_blocking=True)
-            slot["val"][:e - b].copy_(h.val[b:e], non_blocking=True)
-            slot["label"].copy_(h.label[row_start:row_start + B], non_blocking=True)
+            if self.packed:
+                slot["row_len"].copy_(h.row_len[row_start:row_start + B], non_blocking=True)
+                slot["col24"][:3 * (e - b)].copy_(h.col24[3 * b:3 * e], non_blocking=True)
+                slot["val"][:e - b].copy_(h.val[b:e], non_blocking=True)
+                slot["label_u8"].copy_(h.label_u8[row_start:row_start + B], non_blocking=True)
+            else:
+                slot["row_ptr"].copy_(h.row_ptr[row_start:row_start + B + 1], non_blocking=True)
+                slot["col"][:e - b].copy_(h.col[b:e], non_blocking=True)
+                slot["val"][:e - b].copy_(h.val[b:e], non_blocking=True)
+                slot["label"].copy_(h.label[row_start:row_start + B], non_blocking=True)
             slot["ready"].record(self.copy_stream)
-        slot["base"] = b
+        slot["base"] = 0 if self.packed else b
         slot["nnz"] = e - b
-        self.bytes_per_batch = (B + 1) * 8 + (e - b) * 8 + B * 4
+        self.bytes_per_batch = (B + 7 * (e - b) + B) if self.packed else ((B + 1) * 8 + (e - b) * 8 + B * 4)
         return k
 
     def acquire(self, k: int, stream: Optional[torch.cuda.Stream] = None) -> CsrBatchSource:
@@ -64,7 +106,19 @@ class AsyncBatchLoader:
         the ABSOLUTE nnz offsets of the host arrays, so col/val are exposed through pointers
         shifted back by the slot's first offset (see staged_struct)."""
         slot = self.slots[k]
-        (stream or torch.cuda.current_stream()).wait_event(slot["ready"])
+        st = stream or torch.cuda.current_stream()
+        st.wait_event(slot["ready"])
+        if self.packed:
+            # rebuild row_ptr / col / label on the compute stream (three small scan launches + one unpack)
+            import ctypes as C
+            from ..ops import _lib
+            lib = _lib.load()
+            _lib.check(lib.mps_csr_unpack(
+                C.c_void_p(slot["row_len"].data_ptr()), C.c_void_p(slot["col24"].data_ptr()),
+                C.c_void_p(slot["label_u8"].data_ptr()), self.batch, slot["nnz"],
+                C.c_void_p(slot["row_ptr"].data_ptr()), C.c_void_p(slot["col"].data_ptr()),
+                C.c_void_p(slot["label"].data_ptr()), C.c_void_p(slot["scratch"].data_ptr()),
+                _lib.stream_ptr(st)), "csr_unpack")
         return CsrBatchSource(slot["row_ptr"], slot["col"], slot["val"], slot["label"])
 
     def staged_struct(self, k: int):

@@ -126,3 +126,25 @@ def test_hash_backed_map_storage():
         assert total == keys.numel()
     finally:
         engine.stop_everything()
+
+
+def test_packed_batch_loader_matches_plain_csr():
+    """Compact H2D format (u8 row lengths, 24-bit ids, u8 labels) unpacks to exactly the CSR the plain loader stages."""
+    from minips_b200.models.lr import make_synthetic
+    from minips_b200.utils.loader import AsyncBatchLoader, PackedCsrHost
+    data = make_synthetic(20_000, 1_000_000, 40, device="cpu", seed=4)
+    packed = PackedCsrHost.from_csr(data)
+    assert packed is not None
+    B = 4096
+    plain = AsyncBatchLoader(data.pin(), B, "cuda")
+    comp = AsyncBatchLoader(packed, B, "cuda")
+    for start in (0, 1234, 20_000 - B):
+        a = plain.acquire(plain.prefetch(start))
+        b = comp.acquire(comp.prefetch(start))
+        torch.cuda.synchronize()
+        nnz = int(data.row_ptr[start + B] - data.row_ptr[start])
+        assert torch.equal(a.row_ptr - a.row_ptr[0], b.row_ptr)
+        assert torch.equal(a.col[:nnz], b.col[:nnz])
+        assert torch.equal(a.val[:nnz], b.val[:nnz])
+        assert torch.equal(a.label, b.label)
+    assert comp.bytes_per_batch < 0.87 * plain.bytes_per_batch
