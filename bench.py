@@ -136,7 +136,8 @@ def bench_lr_ours(args):
             host_csr = data.to("cpu")
             packed = PackedCsrHost.from_csr(host_csr)
             loader = AsyncBatchLoader(packed if packed is not None else host_csr.pin(), B, dev)
-            result["h2d_format"] = "packed: u8 row_len + u24 col + f32 val + u8 label" if packed is not None else "csr"
+            result["h2d_format"] = (f"packed: u8 row_len + u{packed.id_bits} col + f32 val + u8 label"
+                                    if packed is not None else "csr")
             rs = starts(W + Ke).tolist()
             tr.train_stream(loader, rs[:W])                  # warm-up
             sync_barrier(dev)

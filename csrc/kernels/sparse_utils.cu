@@ -286,9 +286,9 @@ parse_lines_kernel(const char* __restrict__ text, const int64_t* __restrict__ li
 }
 
 // ------------------------------------------------------------------ compact batch format
-// A batch travels host -> device as row lengths (u8), 24-bit feature ids, fp32 values and u8 labels
-// (15 % fewer bytes than int64 row_ptr + int32 ids + fp32 labels; lossless for < 2^24 features and
-// < 256 non-zeros per row).  These kernels rebuild the CSR arrays the training kernels read.
+// A batch travels host -> device as row lengths (u8), feature ids bit-packed at ceil(log2(features)) bits
+// (16 / 20 / 24), fp32 values and u8 labels: 15-20 % fewer bytes than int64 row_ptr + int32 ids + fp32
+// labels, lossless for < 256 non-zeros per row.  These kernels rebuild the CSR arrays the training kernels read.
 struct RowLenU8 {
   const uint8_t* len;
   __device__ uint32_t operator()(int64_t i) const { return len[i]; }
@@ -303,24 +303,28 @@ struct EmitRowPtr64 {
 };
 
 __global__ void __launch_bounds__(256)
-csr_unpack_kernel(const uint32_t* __restrict__ col24_words, int64_t nnz, uint32_t* __restrict__ col,
+csr_unpack_kernel(const uint32_t* __restrict__ words, int id_bits, int bit_off, int64_t nnz, uint32_t* __restrict__ col,
                   const uint8_t* __restrict__ label_u8, int64_t rows, float* __restrict__ label) {
   const int64_t tid = static_cast<int64_t>(blockIdx.x) * blockDim.x + threadIdx.x;
   const int64_t stride = static_cast<int64_t>(gridDim.x) * blockDim.x;
-  // four ids = 12 bytes = three aligned words (the staging buffer starts on a 16-byte boundary)
+  const uint32_t mask = id_bits >= 32 ? 0xffffffffu : ((1u << id_bits) - 1u);
+  // id i occupies bits [bit_off + i * id_bits, +id_bits) of the little-endian stream: two aligned words and a
+  // funnel shift (the staging buffer starts on a 16-byte boundary and has a word of slack at the end)
+  auto id_at = [&](int64_t i) {
+    const int64_t p = bit_off + i * id_bits;
+    const uint32_t lo = words[p >> 5], hi = words[(p >> 5) + 1];
+    return __funnelshift_r(lo, hi, static_cast<uint32_t>(p & 31)) & mask;
+  };
   const int64_t quads = nnz >> 2;
   for (int64_t q = tid; q < quads; q += stride) {
-    const uint32_t w0 = col24_words[3 * q], w1 = col24_words[3 * q + 1], w2 = col24_words[3 * q + 2];
     uint4 o;
-    o.x = w0 & 0xffffffu;
-    o.y = (w0 >> 24) | ((w1 & 0xffffu) << 8);
-    o.z = (w1 >> 16) | ((w2 & 0xffu) << 16);
-    o.w = w2 >> 8;
+    o.x = id_at(4 * q);
+    o.y = id_at(4 * q + 1);
+    o.z = id_at(4 * q + 2);
+    o.w = id_at(4 * q + 3);
     *reinterpret_cast<uint4*>(col + 4 * q) = o;
   }
-  const uint8_t* bytes = reinterpret_cast<const uint8_t*>(col24_words);
-  for (int64_t i = (quads << 2) + tid; i < nnz; i += stride)
-    col[i] = bytes[3 * i] | (static_cast<uint32_t>(bytes[3 * i + 1]) << 8) | (static_cast<uint32_t>(bytes[3 * i + 2]) << 16);
+  for (int64_t i = (quads << 2) + tid; i < nnz; i += stride) col[i] = id_at(i);
   for (int64_t i = tid; i < rows; i += stride) label[i] = static_cast<float>(label_u8[i]);
 }
 
@@ -406,10 +410,12 @@ int mps_libsvm_parse(const char* text, const int64_t* line_end, int64_t n_lines,
   return 0;
 }
 
-int mps_csr_unpack(const uint8_t* row_len, const void* col24, const uint8_t* label_u8, int64_t rows, int64_t nnz,
-                   int64_t* row_ptr, uint32_t* col, float* label, uint32_t* scratch_u32, void* stream) {
+int mps_csr_unpack(const uint8_t* row_len, const void* packed_ids, int id_bits, int bit_off, const uint8_t* label_u8,
+                   int64_t rows, int64_t nnz, int64_t* row_ptr, uint32_t* col, float* label, uint32_t* scratch_u32,
+                   void* stream) {
   if (rows <= 0) return 0;
-  if ((reinterpret_cast<uintptr_t>(col24) & 3) || (reinterpret_cast<uintptr_t>(col) & 15))
+  if ((reinterpret_cast<uintptr_t>(packed_ids) & 3) || (reinterpret_cast<uintptr_t>(col) & 15) || id_bits < 1 ||
+      id_bits > 32 || bit_off < 0 || bit_off > 31)
     return static_cast<int>(cudaErrorInvalidValue);
   auto st = static_cast<cudaStream_t>(stream);
   int rc = mps::exclusive_scan(mps::RowLenU8{row_len}, mps::EmitRowPtr64{row_ptr, rows}, rows, scratch_u32, st);
@@ -418,8 +424,8 @@ int mps_csr_unpack(const uint8_t* row_len, const void* col24, const uint8_t* lab
   int64_t grid = (work + 255) / 256;
   if (grid > 148 * 8) grid = 148 * 8;
   if (grid < 1) grid = 1;
-  mps::csr_unpack_kernel<<<static_cast<unsigned>(grid), 256, 0, st>>>(static_cast<const uint32_t*>(col24), nnz, col,
-                                                                     label_u8, rows, label);
+  mps::csr_unpack_kernel<<<static_cast<unsigned>(grid), 256, 0, st>>>(static_cast<const uint32_t*>(packed_ids), id_bits,
+                                                                     bit_off, nnz, col, label_u8, rows, label);
   MPS_LAUNCH_CHECK();
   return 0;
 }

@@ -236,12 +236,14 @@ int mps_hash_get(const MpsHashView* view, const MpsClockView* clk, int progress,
 int mps_hash_export(const void* keys, const void* vals, int64_t capacity, uint32_t* out_keys,
                     float* out_vals, int* count, void* stream);
 
-/* Rebuild CSR arrays from the compact host->device batch format: row_len [rows] u8, col24 [3*nnz bytes]
- * little-endian 24-bit feature ids (4-byte aligned), label_u8 [rows] in {0,1}  ->  row_ptr [rows+1] int64
- * (starting at 0), col [nnz] u32 (16-byte aligned), label [rows] f32.  scratch_u32: rows/4096 + 2 words. */
-int mps_csr_unpack(const uint8_t* row_len, const void* col24, const uint8_t* label_u8, int64_t rows,
-                   int64_t nnz, int64_t* row_ptr, uint32_t* col, float* label, uint32_t* scratch_u32,
-                   void* stream);
+/* Rebuild CSR arrays from the compact host->device batch format: row_len [rows] u8; packed_ids = a
+ * little-endian bit stream (4-byte aligned, one word of slack after the end) holding nnz feature ids of
+ * id_bits bits each, the first one starting at bit bit_off; label_u8 [rows] in {0,1}  ->  row_ptr
+ * [rows+1] int64 (starting at 0), col [nnz] u32 (16-byte aligned), label [rows] f32.
+ * scratch_u32: rows/4096 + 2 words. */
+int mps_csr_unpack(const uint8_t* row_len, const void* packed_ids, int id_bits, int bit_off,
+                   const uint8_t* label_u8, int64_t rows, int64_t nnz, int64_t* row_ptr, uint32_t* col,
+                   float* label, uint32_t* scratch_u32, void* stream);
 
 /* ---- mini-batch k-means (csrc/kernels/kmeans_tc.cu, kmeans.cu) ----------------------- */
 /* Nearest-centre assignment (apps/kmeans/kmeans_helper.hpp:45-66) as a tcgen05/TMEM/TMA GEMM

@@ -138,7 +138,7 @@ def _declare(lib):
         "mps_libsvm_scan_lines": ([vp, i64, vp, vp, vp, vp], i32),
         "mps_libsvm_index_lines": ([vp, vp, i64, vp, vp, vp, vp, vp, vp, vp, vp], i32),
         "mps_libsvm_parse": ([vp, vp, i64, vp, vp, vp, vp, vp, i32, vp], i32),
-        "mps_csr_unpack": ([vp, vp, vp, i64, i64, vp, vp, vp, vp, vp], i32),
+        "mps_csr_unpack": ([vp, vp, i32, i32, vp, i64, i64, vp, vp, vp, vp, vp], i32),
         "mps_hash_clear": ([vp, vp, i64, vp], i32),
         "mps_hash_add": ([P(HashView), vp, vp, i64, vp, vp], i32),
         "mps_hash_get": ([P(HashView), P(ClockView), i32, vp, vp, i64, vp], i32),

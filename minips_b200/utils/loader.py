@@ -15,14 +15,33 @@ from ..models.lr import CsrBatchSource
 
 
 class PackedCsrHost:
-    """Compact pinned-host form of a CSR data set for the H2D stream: row lengths as u8, feature ids as
-    24-bit little-endian integers, labels as u8, values unchanged (fp32).  Lossless when every row has
-    < 256 non-zeros, every feature id is < 2^24 and labels are 0/1; `from_csr` returns None otherwise."""
+    """Compact pinned-host form of a CSR data set for the H2D stream: row lengths as u8, feature ids
+    bit-packed at 16 / 20 / 24 bits (the smallest that holds every id; little-endian bit stream), labels as
+    u8, values unchanged (fp32).  Lossless when every row has < 256 non-zeros, ids fit 24 bits and labels
+    are 0/1; `from_csr` returns None otherwise."""
 
-    def __init__(self, row_ptr, row_len, col24, val, label_u8):
-        self.row_ptr, self.row_len, self.col24, self.val, self.label_u8 = row_ptr, row_len, col24, val, label_u8
+    def __init__(self, row_ptr, row_len, ids, id_bits, val, label_u8):
+        self.row_ptr, self.row_len, self.ids, self.id_bits = row_ptr, row_len, ids, id_bits
+        self.val, self.label_u8 = val, label_u8
         self.n_rows = row_len.numel()
         self.nnz = val.numel()
+
+    @staticmethod
+    def pack_ids(col: torch.Tensor, id_bits: int) -> torch.Tensor:
+        """int32 ids -> uint8 little-endian bit stream of id_bits per id (plus 8 bytes of slack)."""
+        col = col.to(torch.int32).contiguous()
+        if id_bits == 16:
+            body = col.to(torch.int16).view(torch.uint8)
+        elif id_bits == 24:
+            body = col.view(torch.uint8).view(-1, 4)[:, :3].contiguous().view(-1)
+        elif id_bits == 20:
+            if col.numel() % 2:
+                col = torch.cat([col, col.new_zeros(1)])
+            pairs = col.view(-1, 2).to(torch.int64)
+            body = (pairs[:, 0] | (pairs[:, 1] << 20)).view(torch.uint8).view(-1, 8)[:, :5].contiguous().view(-1)
+        else:
+            raise ValueError(id_bits)
+        return torch.cat([body, body.new_zeros(8)])
 
     @staticmethod
     def from_csr(host: CsrBatchSource) -> "Optional[PackedCsrHost]":
@@ -30,12 +49,14 @@ class PackedCsrHost:
         lens = rp[1:] - rp[:-1]
         col = host.col.cpu()
         lab = host.label.cpu()
-        if int(lens.max()) > 255 or int(col.max()) >= (1 << 24) or int(col.min()) < 0:
+        cmax = int(col.max()) if col.numel() else 0
+        if int(lens.max()) > 255 or cmax >= (1 << 24) or int(col.min()) < 0:
             return None
         if not bool(((lab == 0) | (lab == 1)).all()):
             return None
-        col24 = col.to(torch.int32).contiguous().view(torch.uint8).view(-1, 4)[:, :3].contiguous().view(-1)
-        return PackedCsrHost(rp.contiguous(), lens.to(torch.uint8).pin_memory(), col24.pin_memory(),
+        id_bits = 16 if cmax < (1 << 16) else (20 if cmax < (1 << 20) else 24)
+        return PackedCsrHost(rp.contiguous(), lens.to(torch.uint8).pin_memory(),
+                             PackedCsrHost.pack_ids(col, id_bits).pin_memory(), id_bits,
                              host.val.cpu().contiguous().pin_memory(), lab.to(torch.uint8).pin_memory())
 
 
@@ -43,7 +64,7 @@ class AsyncBatchLoader:
     def __init__(self, host, batch: int, device, depth: int = 2):
         self.packed = isinstance(host, PackedCsrHost)
         if self.packed:
-            assert host.row_len.is_pinned() and host.col24.is_pinned() and host.val.is_pinned() and host.label_u8.is_pinned()
+            assert host.row_len.is_pinned() and host.ids.is_pinned() and host.val.is_pinned() and host.label_u8.is_pinned()
         else:
             assert host.row_ptr.is_pinned() and host.col.is_pinned() and host.val.is_pinned() and host.label.is_pinned()
         self.host = host
@@ -67,7 +88,7 @@ class AsyncBatchLoader:
             if self.packed:
                 self.slots[-1].update({
                     "row_len": torch.empty(batch, dtype=torch.uint8, device=device),
-                    "col24": torch.empty(3 * max_nnz + 16, dtype=torch.uint8, device=device),
+                    "ids": torch.empty((max_nnz * host.id_bits + 7) // 8 + 16, dtype=torch.uint8, device=device),
                     "label_u8": torch.empty(batch, dtype=torch.uint8, device=device),
                     "scratch": torch.empty(batch // 4096 + 4, dtype=torch.int32, device=device),
                 })
@@ -87,7 +108,11 @@ class AsyncBatchLoader:
                 self.copy_stream.wait_event(slot["free"])
             if self.packed:
                 slot["row_len"].copy_(h.row_len[row_start:row_start + B], non_blocking=True)
-                slot["col24"][:3 * (e - b)].copy_(h.col24[3 * b:3 * e], non_blocking=True)
+                w = h.id_bits
+                byte0, byte1 = (b * w) // 8, (e * w + 7) // 8 + 4   # + the word of slack the unpack kernel may touch
+                slot["ids"][:byte1 - byte0].copy_(h.ids[byte0:byte1], non_blocking=True)
+                slot["bit_off"] = (b * w) % 8
+                slot["id_bytes"] = byte1 - byte0
                 slot["val"][:e - b].copy_(h.val[b:e], non_blocking=True)
                 slot["label_u8"].copy_(h.label_u8[row_start:row_start + B], non_blocking=True)
             else:
@@ -98,7 +123,8 @@ class AsyncBatchLoader:
             slot["ready"].record(self.copy_stream)
         slot["base"] = 0 if self.packed else b
         slot["nnz"] = e - b
-        self.bytes_per_batch = (B + 7 * (e - b) + B) if self.packed else ((B + 1) * 8 + (e - b) * 8 + B * 4)
+        self.bytes_per_batch = (B + slot["id_bytes"] + 4 * (e - b) + B) if self.packed else \
+            ((B + 1) * 8 + (e - b) * 8 + B * 4)
         return k
 
     def acquire(self, k: int, stream: Optional[torch.cuda.Stream] = None) -> CsrBatchSource:
@@ -114,8 +140,8 @@ class AsyncBatchLoader:
             from ..ops import _lib
             lib = _lib.load()
             _lib.check(lib.mps_csr_unpack(
-                C.c_void_p(slot["row_len"].data_ptr()), C.c_void_p(slot["col24"].data_ptr()),
-                C.c_void_p(slot["label_u8"].data_ptr()), self.batch, slot["nnz"],
+                C.c_void_p(slot["row_len"].data_ptr()), C.c_void_p(slot["ids"].data_ptr()), self.host.id_bits,
+                slot["bit_off"], C.c_void_p(slot["label_u8"].data_ptr()), self.batch, slot["nnz"],
                 C.c_void_p(slot["row_ptr"].data_ptr()), C.c_void_p(slot["col"].data_ptr()),
                 C.c_void_p(slot["label"].data_ptr()), C.c_void_p(slot["scratch"].data_ptr()),
                 _lib.stream_ptr(st)), "csr_unpack")

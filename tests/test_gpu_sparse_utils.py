@@ -128,23 +128,32 @@ def test_hash_backed_map_storage():
         engine.stop_everything()
 
 
-def test_packed_batch_loader_matches_plain_csr():
-    """Compact H2D format (u8 row lengths, 24-bit ids, u8 labels) unpacks to exactly the CSR the plain loader stages."""
-    from minips_b200.models.lr import make_synthetic
+@pytest.mark.parametrize("features", [50_000, 1_000_000, 5_000_000])
+def test_packed_batch_loader_matches_plain_csr(features):
+    """Compact H2D format (u8 row lengths, 16/20/24-bit ids, u8 labels) unpacks to exactly the CSR the plain
+    loader stages; rows of varying length make the windows start at odd nnz offsets (bit offset 4 at 20 bits)."""
+    from minips_b200.models.lr import CsrBatchSource
     from minips_b200.utils.loader import AsyncBatchLoader, PackedCsrHost
-    data = make_synthetic(20_000, 1_000_000, 40, device="cpu", seed=4)
+    g = torch.Generator().manual_seed(4)
+    n = 20_000
+    lens = torch.randint(1, 60, (n,), generator=g)
+    row_ptr = torch.zeros(n + 1, dtype=torch.int64)
+    row_ptr[1:] = torch.cumsum(lens, 0)
+    nnz = int(row_ptr[-1])
+    data = CsrBatchSource(row_ptr, torch.randint(0, features, (nnz,), generator=g, dtype=torch.int32),
+                          torch.randn(nnz, generator=g), torch.randint(0, 2, (n,), generator=g).float())
     packed = PackedCsrHost.from_csr(data)
-    assert packed is not None
+    assert packed is not None and packed.id_bits == {50_000: 16, 1_000_000: 20, 5_000_000: 24}[features]
     B = 4096
     plain = AsyncBatchLoader(data.pin(), B, "cuda")
     comp = AsyncBatchLoader(packed, B, "cuda")
-    for start in (0, 1234, 20_000 - B):
+    for start in (0, 1, 1234, 7777, n - B):
         a = plain.acquire(plain.prefetch(start))
         b = comp.acquire(comp.prefetch(start))
         torch.cuda.synchronize()
-        nnz = int(data.row_ptr[start + B] - data.row_ptr[start])
+        m = int(row_ptr[start + B] - row_ptr[start])
         assert torch.equal(a.row_ptr - a.row_ptr[0], b.row_ptr)
-        assert torch.equal(a.col[:nnz], b.col[:nnz])
-        assert torch.equal(a.val[:nnz], b.val[:nnz])
+        assert torch.equal(a.col[:m], b.col[:m])
+        assert torch.equal(a.val[:m], b.val[:m])
         assert torch.equal(a.label, b.label)
     assert comp.bytes_per_batch < 0.87 * plain.bytes_per_batch
