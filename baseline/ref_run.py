@@ -16,6 +16,14 @@ REF_BIN = os.path.join(ROOT, "baseline", "_ref", "bin", "LRExample")
 
 
 def run(args):
+    if getattr(args, "app", "lr") == "kmeans":
+        if int(os.environ.get("RANK", "0")) != 0:
+            return None
+        return {"impl": "reference",
+                "unavailable": "the reference KMeans app cannot run K=1024, d=128: it stores the per-centre counts in "
+                               "params[K][i], a row of num_dims entries (kmeans_helper.hpp:41, needs K <= num_dims), and "
+                               "its random_init re-seeds rand() with time(NULL) per draw (one centre per second); see "
+                               "BASELINE.md section 3"}
     if not os.path.exists(REF_BIN):
         if int(os.environ.get("RANK", "0")) != 0:
             return None
