@@ -175,3 +175,22 @@ def test_device_barrier_single_rank(engine):
 
     _run(engine, tid, fn)
     assert engine.tables[tid].barrier_epoch == 3
+
+
+def test_straggle_and_phase_timer():
+    """mps_straggle holds the stream for the requested time; PhaseTimer attributes it to its phase."""
+    import ctypes as C
+    from minips_b200.ops import _lib
+    from minips_b200.utils.tracing import PhaseTimer
+    lib = _lib.load()
+    pt = PhaseTimer()
+    x = torch.zeros(1 << 20, device="cuda")
+    for _ in range(3):
+        with pt.phase("straggle"):
+            _lib.check(lib.mps_straggle(C.c_longlong(2_000_000), _lib.stream_ptr()), "straggle")
+        with pt.phase("work"):
+            x.add_(1.0)
+    s = pt.summary("cuda", reduce_over_ranks=False)
+    assert s["straggle"]["calls"] == 3 and s["work"]["calls"] == 3
+    assert 6.0 <= s["straggle"]["ms"] < 30.0, s
+    assert s["work"]["ms"] < s["straggle"]["ms"]
