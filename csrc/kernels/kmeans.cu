@@ -148,7 +148,7 @@ constexpr int kSortedRun = 64;  // sorted rows per unit
 // in flight.  All loops have warp-uniform trip counts (rows past the end are predicated off) so the
 // shuffles stay convergent while units flush at different positions.
 template <int D>
-__global__ void __launch_bounds__(256)
+__global__ void __launch_bounds__(256, 3)
 kmeans_sorted_sum_kernel(const __nv_bfloat16* __restrict__ x, const int32_t* __restrict__ perm,
                          const int* __restrict__ base, const float* __restrict__ dist, int K,
                          float* __restrict__ sums, float* __restrict__ sse) {
@@ -188,21 +188,21 @@ kmeans_sorted_sum_kernel(const __nv_bfloat16* __restrict__ x, const int32_t* __r
 #pragma unroll
       for (int j0 = 0; j0 < LPR; j0 += U) {
         uint4 raw[U];
-        int idx[U];
 #pragma unroll
         for (int u = 0; u < U; ++u) {
-          idx[u] = __shfl_sync(0xffffffffu, mine, ubase + j0 + u);
+          const int idx = __shfl_sync(0xffffffffu, mine, ubase + j0 + u);
           raw[u] = make_uint4(0u, 0u, 0u, 0u);
-          if (idx[u] >= 0) raw[u] = *reinterpret_cast<const uint4*>(x + static_cast<int64_t>(idx[u]) * D + sub * 8);
+          if (idx >= 0) raw[u] = *reinterpret_cast<const uint4*>(x + static_cast<int64_t>(idx) * D + sub * 8);
         }
 #pragma unroll
         for (int u = 0; u < U; ++u) {
           const int pos = r0 + b0 + j0 + u;
+          const bool valid = pos < r1;  // rows past the end of the unit's run were loaded as zeros
           const float2 p0 = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162*>(&raw[u].x));
           const float2 p1 = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162*>(&raw[u].y));
           const float2 p2 = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162*>(&raw[u].z));
           const float2 p3 = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162*>(&raw[u].w));
-          if (idx[u] >= 0 && pos >= next) {  // this unit's run crosses into another centre
+          if (valid && pos >= next) {  // this unit's run crosses into another centre
             float* dst = sums + static_cast<int64_t>(c) * D + sub * 8;
             red_gpu_v4(dst, make_float4(acc[0], acc[1], acc[2], acc[3]));
             red_gpu_v4(dst + 4, make_float4(acc[4], acc[5], acc[6], acc[7]));
@@ -217,7 +217,7 @@ kmeans_sorted_sum_kernel(const __nv_bfloat16* __restrict__ x, const int32_t* __r
 #pragma unroll
           for (int o = LPR / 2; o > 0; o >>= 1) xn += __shfl_xor_sync(0xffffffffu, xn, o);
           const float d = __shfl_sync(0xffffffffu, my_dist, ubase + j0 + u);
-          if (sub == 0 && idx[u] >= 0) local_sse += fmaxf(xn + d, 0.f);
+          if (sub == 0 && valid) local_sse += fmaxf(xn + d, 0.f);
         }
       }
     }
