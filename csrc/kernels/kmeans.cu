@@ -9,6 +9,8 @@
 // centres (what the tensor-core kernel needs) and the push is one dense slab.
 #include <cuda_bf16.h>
 
+#include <cstdlib>
+
 #include "common.cuh"
 
 namespace mps {
@@ -140,6 +142,10 @@ kmeans_scatter_kernel(const int32_t* __restrict__ assign, int64_t n, int K, int*
     if (a >= 0 && a < K) perm[start[a] + atomicAdd(&cnt[a], 1)] = static_cast<int32_t>(i);
   }
 }
+
+}  // namespace mps
+#include "kmeans_runsum_bulk.cuh"
+namespace mps {
 
 constexpr int kSortedRun = 64;  // sorted rows per unit
 
@@ -354,7 +360,24 @@ int mps_kmeans_accumulate_sorted(const void* x_bf16, const int32_t* assign, cons
   const int upw = 32 / (D / 8);                       // units per warp
   const int64_t ctas = (runs + 8 * upw - 1) / (8 * upw);
   const int g2 = static_cast<int>(ctas < sms * 8 ? ctas : sms * 8);
-  if (D == 128)
+  // MINIPS_RUNSUM=bulk selects the copy-engine version (kmeans_runsum_bulk.cuh); measured slower, see there
+  static int use_bulk = -1;
+  if (use_bulk < 0) {
+    const char* e = getenv("MINIPS_RUNSUM");
+    use_bulk = (e && e[0] == 'b') ? 1 : 0;
+    if (use_bulk && cudaFuncSetAttribute(mps::kmeans_runsum_bulk_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                         mps::kBulkSmem) != cudaSuccess) {
+      cudaGetLastError();
+      use_bulk = 0;
+    }
+  }
+  if (D == 128 && use_bulk) {
+    const int64_t bruns = (n + mps::kBulkRun - 1) / mps::kBulkRun;
+    const int64_t bctas = (bruns + mps::kBulkWarps - 1) / mps::kBulkWarps;
+    const int bg = static_cast<int>(bctas < sms * 3 ? bctas : sms * 3);
+    mps::kmeans_runsum_bulk_kernel<<<bg, mps::kBulkWarps * 32, mps::kBulkSmem, st>>>(
+        static_cast<const __nv_bfloat16*>(x_bf16), perm, base, dist, K, sums, sse);
+  } else if (D == 128)
     mps::kmeans_sorted_sum_kernel<128><<<g2, 256, 0, st>>>(static_cast<const __nv_bfloat16*>(x_bf16), perm, base, dist,
                                                           K, sums, sse);
   else
