@@ -90,3 +90,14 @@ def test_tracing_helpers_are_noops_without_cuda_or_flag():
     with pt.phase("p"):
         pass
     assert pt.summary() == {}
+
+
+def test_packed_ids_bit_stream_round_trips():
+    """Loader's compact id stream: ids at 16 / 20 / 24 bits, little-endian, decodable at any start offset."""
+    import torch
+    from minips_b200.utils.loader import PackedCsrHost
+    for bits, top in ((16, 60_000), (20, 1_000_000), (24, 10_000_000)):
+        col = torch.randint(0, top, (1001,), dtype=torch.int32)
+        stream = int.from_bytes(PackedCsrHost.pack_ids(col, bits).numpy().tobytes(), "little")
+        got = [(stream >> (i * bits)) & ((1 << bits) - 1) for i in range(col.numel())]
+        assert got == col.tolist(), bits
