@@ -13,7 +13,9 @@
 #include <chrono>
 #include <cmath>
 #include <iostream>
+#include <mutex>
 #include <random>
+#include <sstream>
 
 #include "core/checkpoint_io.hpp"
 #include "core/driver.hpp"
@@ -140,6 +142,7 @@ static int Training(const Node& my_node, const std::vector<Node>& nodes, const N
   for (const auto& n : engine.GetNodes()) alloc.push_back({n.id, static_cast<uint32_t>(ctx.get_int32("num_workers_per_node"))});
   task.SetWorkerAlloc(alloc);
   task.SetTables({table});
+  std::mutex print_mu;
   task.SetLambda([&](const Info& info) {
     lib::BatchDataSampler<SVMItem> sampler(data, batch, static_cast<uint64_t>(ctx.get_int32("seed")) * 1000 + info.worker_id + 1);
     // all batches up front, like lr_example.cpp:231-236
@@ -212,10 +215,16 @@ static int Training(const Node& my_node, const std::vector<Node>& nodes, const N
       for (int k = 0; k < num_dims; ++k) all[k] = static_cast<Key>(k);
       std::vector<double> w;
       t->Get(all, &w);
-      std::cout << "[node " << my_node.id << "] accuracy " << TestAccuracy(w, data) << " on " << data.size()
-                << " local samples" << std::endl;
+      std::ostringstream line;
+      line << "[node " << my_node.id << "] accuracy " << TestAccuracy(w, data) << " on " << data.size()
+           << " local samples\n";
+      std::lock_guard<std::mutex> lk(print_mu);  // worker threads share std::cout: one line, one write
+      std::cout << line.str() << std::flush;
     }
-    std::cout << "Total training time: " << total << " ms on worker " << info.worker_id << std::endl;
+    std::ostringstream line;
+    line << "Total training time: " << total << " ms on worker " << info.worker_id << "\n";
+    std::lock_guard<std::mutex> lk(print_mu);
+    std::cout << line.str() << std::flush;
   });
   engine.Run(task);
   engine.StopEverything();
