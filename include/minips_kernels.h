@@ -139,7 +139,7 @@ typedef struct MpsCsr {
  * [row_begin, row_begin + batch) modulo n_rows (BatchDataSampler wrap-around,
  * lib/batch_data_sampler.cpp:50-71).  loss_out[0] += sum logloss, loss_out[1] += #correct. */
 int mps_lr_step_sparse(const MpsTableView* view, const MpsClockView* clk, int worker, int progress,
-                       const MpsCsr* csr, int64_t row_begin, int64_t batch, float alpha,
+                       const MpsCsr* csr, int64_t row_begin, int64_t batch, double alpha,
                        float* loss_out, void* stream);
 
 /* Dense regime, persistent cooperative kernel running `n_iters` whole iterations
@@ -151,18 +151,50 @@ int mps_lr_step_sparse(const MpsTableView* view, const MpsClockView* clk, int wo
  * before the first iteration. */
 int mps_lr_train_dense(const MpsTableView* view, const MpsClockView* clk, int worker,
                        int start_clock, const MpsCsr* csr, const int64_t* batch_starts,
-                       int n_iters, int64_t batch, float alpha, float* replica, float* gacc,
+                       int n_iters, int64_t batch, double alpha, void* replica, void* gacc,
                        float* loss_out, int max_ctas, void* stream);
 
 /* mps_lr_train_dense plus observability / tuning knobs: `timeline` (NULL or 8 uint64 per
  * iteration) receives %globaltimer at the phase boundaries gate|pull|sync1|rows+sync2|
  * pulled-wait|push (the per-phase timers SURVEY 5.1 asks for); avg_nnz picks the lanes per
- * row (8/16/32; 0 = 40 nnz default). */
+ * row (8/16/32; 0 = 40 nnz default).
+ * Both take fp32 or fp64 tables (view->dtype; replica / gacc are of the table's type) — the
+ * reference runs every table as Val = double (worker/kv_client_table.hpp:98-99).  Feature ids
+ * outside the table's key range are skipped (range_partition_manager.hpp:24-41 drops them).
+ * One dense-training worker per GPU and table: the kernel is a full-occupancy cooperative
+ * launch that spins on its peers' clocks, so two of them cannot share a device. */
 int mps_lr_train_dense_ex(const MpsTableView* view, const MpsClockView* clk, int worker,
                           int start_clock, const MpsCsr* csr, const int64_t* batch_starts,
-                          int n_iters, int64_t batch, float alpha, float* replica, float* gacc,
+                          int n_iters, int64_t batch, double alpha, void* replica, void* gacc,
                           float* loss_out, unsigned long long* timeline, int avg_nnz, int max_ctas,
                           void* stream);
+
+/* BSP iterations as one exchange per step — reduce at the owner, owner broadcasts
+ * (csrc/kernels/lr_xchg.cu; semantics of server/consistency/bsp_model.cpp:14-43: adds of a
+ * clock become visible only after every worker clocked).  Every rank keeps a full weight
+ * replica and two gradient accumulators in a symmetric buffer; replica[r] / gacc[r] address
+ * rank r's copies from this device, replica_mc / gacc_mc are the NVLS multicast addresses of
+ * the same buffers (NULL: plain peer loads / stores instead of multimem.ld_reduce /
+ * multimem.st).  gacc_stride = elements between a rank's two accumulators.  replica_valid != 0
+ * promises that the replica already holds the weights of start_clock (the previous launch on
+ * this table ended there and nothing else wrote the table since); otherwise the kernel waits
+ * for the Get gate and copies every shard once.
+ * Collective: every rank of the table runs exactly one worker through this call with the same
+ * n_iters; BSP tables with one value per key; fp32 or fp64.  timeline slots per iteration:
+ * start | gate | rows+barrier | owner-wait | reduce+broadcast | fold-signal. */
+typedef struct MpsXchg {
+  void* replica[MPS_MAX_RANKS];
+  void* gacc[MPS_MAX_RANKS];
+  void* replica_mc;
+  void* gacc_mc;
+  int64_t gacc_stride;
+  int32_t replica_valid;
+  int32_t reserved;
+} MpsXchg;
+int mps_lr_train_xchg(const MpsTableView* view, const MpsClockView* clk, int worker, int start_clock,
+                      const MpsCsr* csr, const int64_t* batch_starts, int n_iters, int64_t batch,
+                      double alpha, const MpsXchg* xchg, float* loss_out, unsigned long long* timeline,
+                      int avg_nnz, int max_ctas, void* stream);
 
 /* The same persistent training kernel as mps_lr_train_dense, for callers that cannot
  * allocate device memory.  (No counterpart in the reference: its workers allocate freely
@@ -189,9 +221,10 @@ int mps_lr_train_dense_noalloc(const MpsTableView* view, const MpsClockView* clk
                                void* stream);
 
 /* Accuracy / logloss of local rows against a local full copy of the weights
- * (lr_example.cpp:61-87).  out[0] += logloss, out[1] += #correct. */
-int mps_lr_eval(const float* weights, const MpsCsr* csr, int64_t row_begin, int64_t n,
-                float* out, void* stream);
+ * (lr_example.cpp:61-87): weights[k - key0] for keys [key0, key0 + n_keys), dtype MPS_F32 /
+ * MPS_F64; feature ids outside that range are skipped.  out[0] += logloss, out[1] += #correct. */
+int mps_lr_eval(const void* weights, int dtype, uint32_t key0, uint32_t n_keys, const MpsCsr* csr,
+                int64_t row_begin, int64_t n, float* out, void* stream);
 
 /* ---- sparse helpers (csrc/kernels/sparse_utils.cu) ----------------------------------- */
 /* Sorted unique feature ids of a batch (lib/batch_data_sampler.cpp:50-71) and, optionally,

@@ -84,8 +84,36 @@ def make_synthetic(n_rows: int, n_features: int, nnz_per_row: int = 40, device="
     return CsrBatchSource(row_ptr, col, val, label)
 
 
+class XchgScratch:
+    """Symmetric scratch of the reduce-at-owner / owner-broadcasts kernel (csrc/kernels/lr_xchg.cu):
+    per rank one weight replica and two gradient accumulators, mapped by every peer and — when the
+    fabric has NVLS — by the switch as one multicast address.  Creating it is collective."""
+
+    def __init__(self, table: DeviceTable):
+        from ..parallel.heap import SymmetricBuffer
+        n = table.num_keys
+        self.stride_bytes = (n * table.itemsize + 255) // 256 * 256
+        self.buf = SymmetricBuffer(3 * self.stride_bytes, table.control, table.device, multicast=True)
+        x = _lib.Xchg()
+        for r in range(table.world):
+            x.replica[r] = self.buf.ptrs[r]
+            x.gacc[r] = self.buf.ptrs[r] + self.stride_bytes
+        x.replica_mc = self.buf.mc_ptr or None
+        x.gacc_mc = (self.buf.mc_ptr + self.stride_bytes) if self.buf.mc_ptr else None
+        x.gacc_stride = self.stride_bytes // table.itemsize
+        self.c = x
+        self.multicast = bool(self.buf.mc_ptr)
+        self.valid_clock = -1       # clock whose weights the local replica holds
+        self.valid_epoch = -1       # table.write_epoch at that time
+        self.replica = self.buf.local_tensor(0, n, table.dtype)
+
+    def close(self):
+        self.buf.close()
+
+
 class SparseLRTrainer:
-    """Device trainer bound to one worker's KVClientTable."""
+    """Device trainer bound to one worker's KVClientTable (fp32 or fp64 tables; the reference's
+    tables are Val = double, lr_example.cpp:182)."""
 
     def __init__(self, client: KVClientTable, data: CsrBatchSource, alpha: float = 0.1):
         self.client = client
@@ -97,13 +125,13 @@ class SparseLRTrainer:
         self._replica: Optional[torch.Tensor] = None
         self._gacc: Optional[torch.Tensor] = None
         self.avg_nnz = max(1, int(round(data.nnz / max(1, data.n_rows))))
-        assert self.table.dtype == torch.float32 and self.table.k == 1
+        assert self.table.dtype in (torch.float32, torch.float64) and self.table.k == 1
 
     def _scratch(self):
         if self._replica is None:
             n = self.table.num_keys
-            self._replica = torch.empty(n, dtype=torch.float32, device=self.dev)
-            self._gacc = torch.zeros(n, dtype=torch.float32, device=self.dev)
+            self._replica = torch.empty(n, dtype=self.table.dtype, device=self.dev)
+            self._gacc = torch.zeros(n, dtype=self.table.dtype, device=self.dev)
         return self._replica, self._gacc
 
     def dense_regime(self, batch: int) -> bool:
@@ -111,16 +139,37 @@ class SparseLRTrainer:
         nnz_per_row = max(1, self.data.nnz // max(1, self.data.n_rows))
         return batch * nnz_per_row * 4 >= self.table.num_keys
 
+    def xchg_ok(self) -> bool:
+        """The one-exchange-per-step kernel needs BSP and exactly one worker on every rank of the
+        table, all training through it in lockstep."""
+        t = self.table
+        return (t.model_type == ModelType.BSP and t.num_workers == t.world and len(t.local_workers) == 1
+                and t.hview is None)
+
+    def _xchg(self) -> XchgScratch:
+        t = self.table
+        if getattr(t, "xchg", None) is None:
+            t.xchg = XchgScratch(t)        # collective: every rank reaches its first fused launch together
+        return t.xchg
+
     @traced("lr.train_dense")
     def train_dense(self, batch_starts: torch.Tensor, batch: int, max_ctas: int = 0,
                     csr: Optional[_lib.Csr] = None, loss: Optional[torch.Tensor] = None,
-                    timeline: Optional[torch.Tensor] = None) -> torch.Tensor:
+                    timeline: Optional[torch.Tensor] = None, protocol: str = "auto") -> torch.Tensor:
         """Run len(batch_starts) iterations inside one persistent kernel.  Returns the per-
-        iteration (logloss sum, #correct) tensor [n_iters, 2] (device, async)."""
+        iteration (logloss sum, #correct) tensor [n_iters, 2] (device, async).
+
+        protocol: "xchg" = reduce at the owner, owner broadcasts (BSP, one worker per rank);
+        "pushpull" = slab pull / slab push per iteration (any consistency model); "auto" picks
+        xchg whenever it applies.  Between two xchg launches on a table the OTHER ranks must not
+        Add through the generic path (this rank's own generic writes are noticed and the replica
+        is refreshed)."""
         c = self.client
         t = self.table
+        if len(t.local_workers) > 1:
+            raise RuntimeError("dense LR training is a full-occupancy cooperative kernel: one dense-training "
+                               "worker per GPU and table (use step_sparse with several local workers)")
         n_iters = int(batch_starts.numel())
-        replica, gacc = self._scratch()
         if loss is None:
             loss = torch.zeros(n_iters, 2, dtype=torch.float32, device=self.dev)
         cv = t.clock_view()
@@ -128,11 +177,25 @@ class SparseLRTrainer:
             csr = self.data.c_struct()
         c._local_gate()
         tl_ptr = C.c_void_p(timeline.data_ptr()) if timeline is not None else None
-        _lib.check(self.lib.mps_lr_train_dense_ex(
-            C.byref(t.view), C.byref(cv), c.worker_id, c.progress, C.byref(csr),
-            C.c_void_p(batch_starts.data_ptr()), n_iters, batch, self.alpha,
-            C.c_void_p(replica.data_ptr()), C.c_void_p(gacc.data_ptr()), C.c_void_p(loss.data_ptr()),
-            tl_ptr, self.avg_nnz, max_ctas, c._sp()), "lr_train_dense")
+        use_xchg = protocol == "xchg" or (protocol == "auto" and self.xchg_ok())
+        if use_xchg:
+            assert self.xchg_ok(), "xchg protocol: BSP table with exactly one worker on every rank"
+            x = self._xchg()
+            x.c.replica_valid = int(x.valid_clock == c.progress and x.valid_epoch == t.write_epoch)
+            _lib.check(self.lib.mps_lr_train_xchg(
+                C.byref(t.view), C.byref(cv), c.worker_id, c.progress, C.byref(csr),
+                C.c_void_p(batch_starts.data_ptr()), n_iters, batch, self.alpha, C.byref(x.c),
+                C.c_void_p(loss.data_ptr()), tl_ptr, self.avg_nnz, max_ctas, c._sp()), "lr_train_xchg")
+            x.valid_clock = c.progress + n_iters
+            x.valid_epoch = t.write_epoch
+        else:
+            replica, gacc = self._scratch()
+            _lib.check(self.lib.mps_lr_train_dense_ex(
+                C.byref(t.view), C.byref(cv), c.worker_id, c.progress, C.byref(csr),
+                C.c_void_p(batch_starts.data_ptr()), n_iters, batch, self.alpha,
+                C.c_void_p(replica.data_ptr()), C.c_void_p(gacc.data_ptr()), C.c_void_p(loss.data_ptr()),
+                tl_ptr, self.avg_nnz, max_ctas, c._sp()), "lr_train_dense")
+            t.write_epoch += 1      # in-place adds: a replica kept by the xchg kernel is stale now
         # host mirror of the clock (the kernel published the device-side one)
         with t.lock:
             c.progress += n_iters
@@ -180,6 +243,7 @@ class SparseLRTrainer:
         _lib.check(self.lib.mps_lr_step_sparse(
             C.byref(t.view), C.byref(cv), c.worker_id, c.progress, C.byref(csr), row_begin, batch,
             self.alpha, C.c_void_p(loss.data_ptr()), c._sp()), "lr_step_sparse")
+        t.write_epoch += 1
         c.clock()
         return loss
 
@@ -190,7 +254,10 @@ class SparseLRTrainer:
         n = self.data.n_rows if n is None else n
         out = torch.zeros(2, dtype=torch.float32, device=self.dev)
         csr = self.data.c_struct()
-        _lib.check(self.lib.mps_lr_eval(C.c_void_p(weights.data_ptr()), C.byref(csr), 0, n,
+        t = self.table
+        assert weights.dtype == t.dtype and weights.numel() == t.num_keys
+        _lib.check(self.lib.mps_lr_eval(C.c_void_p(weights.data_ptr()), _lib.F32 if t.dtype == torch.float32 else _lib.F64,
+                                        t.ranges[0][0], t.num_keys, C.byref(csr), 0, n,
                                         C.c_void_p(out.data_ptr()), self.client._sp()), "lr_eval")
         o = out.tolist()
         return o[0] / n, o[1] / n
@@ -213,8 +280,9 @@ def oracle_step(w: torch.Tensor, data: CsrBatchSource, row_begin: int, batch: in
     nz = torch.repeat_interleave(starts, lens) + offs
     cols = data.col[nz].to(torch.int64) & 0xFFFFFFFF
     vals = data.val[nz]
-    z = torch.zeros(batch, dtype=torch.float32, device=w.device).index_add_(0, row_of, w[cols] * vals)
-    y = data.label[idx]
+    z = torch.zeros(batch, dtype=w.dtype, device=w.device).index_add_(0, row_of, w[cols] * vals.to(w.dtype))
+    y = data.label[idx].to(w.dtype)
+    vals = vals.to(w.dtype)
     pred = torch.sigmoid(z)
     g = alpha * (y - pred)
     delta = torch.zeros_like(w).index_add_(0, cols, g[row_of] * vals)

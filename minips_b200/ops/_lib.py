@@ -63,6 +63,19 @@ class Csr(C.Structure):
     ]
 
 
+class Xchg(C.Structure):
+    """MpsXchg: symmetric scratch of the reduce-at-owner / owner-broadcasts LR kernel."""
+    _fields_ = [
+        ("replica", C.c_void_p * MAX_RANKS),
+        ("gacc", C.c_void_p * MAX_RANKS),
+        ("replica_mc", C.c_void_p),
+        ("gacc_mc", C.c_void_p),
+        ("gacc_stride", C.c_int64),
+        ("replica_valid", C.c_int32),
+        ("reserved", C.c_int32),
+    ]
+
+
 class HashView(C.Structure):
     _fields_ = [
         ("keys", C.c_void_p * MAX_SHARDS),
@@ -106,7 +119,7 @@ def load(build_if_missing: bool = True):
 
 
 def _declare(lib):
-    vp, i32, i64, f32 = C.c_void_p, C.c_int, C.c_int64, C.c_float
+    vp, i32, i64, f32, f64 = C.c_void_p, C.c_int, C.c_int64, C.c_float, C.c_double
     P = C.POINTER
     sig = {
         "mps_device_count": ([], i32),
@@ -128,12 +141,14 @@ def _declare(lib):
         "mps_barrier": ([P(ClockView), i32, vp], i32),
         "mps_reset_pad": ([P(ClockView), i32, vp], i32),
         "mps_straggle": ([C.c_longlong, vp], i32),
-        "mps_lr_step_sparse": ([P(TableView), P(ClockView), i32, i32, P(Csr), i64, i64, f32, vp, vp], i32),
-        "mps_lr_train_dense": ([P(TableView), P(ClockView), i32, i32, P(Csr), vp, i32, i64, f32, vp, vp, vp,
+        "mps_lr_step_sparse": ([P(TableView), P(ClockView), i32, i32, P(Csr), i64, i64, f64, vp, vp], i32),
+        "mps_lr_train_dense": ([P(TableView), P(ClockView), i32, i32, P(Csr), vp, i32, i64, f64, vp, vp, vp,
                                 i32, vp], i32),
-        "mps_lr_train_dense_ex": ([P(TableView), P(ClockView), i32, i32, P(Csr), vp, i32, i64, f32, vp, vp, vp,
+        "mps_lr_train_dense_ex": ([P(TableView), P(ClockView), i32, i32, P(Csr), vp, i32, i64, f64, vp, vp, vp,
                                    vp, i32, i32, vp], i32),
-        "mps_lr_eval": ([vp, P(Csr), i64, i64, vp, vp], i32),
+        "mps_lr_train_xchg": ([P(TableView), P(ClockView), i32, i32, P(Csr), vp, i32, i64, f64, P(Xchg), vp, vp,
+                               i32, i32, vp], i32),
+        "mps_lr_eval": ([vp, i32, C.c_uint32, C.c_uint32, P(Csr), i64, i64, vp, vp], i32),
         "mps_batch_unique_keys": ([P(Csr), i64, i64, C.c_uint32, vp, vp, vp, vp, i64, vp], i32),
         "mps_libsvm_scan_lines": ([vp, i64, vp, vp, vp, vp], i32),
         "mps_libsvm_index_lines": ([vp, vp, i64, vp, vp, vp, vp, vp, vp, vp, vp], i32),

@@ -141,6 +141,9 @@ class DeviceTable:
         self.local_clock: Dict[int, int] = {}     # worker -> enqueued clock (host mirror)
         self.local_events: Dict[int, torch.cuda.Event] = {}
         self.local_workers: List[int] = []
+        self.ckpt_barrier = threading.Barrier(1)
+        self.write_epoch = 0      # bumped by every local write that bypasses a fused kernel's replica
+        self.xchg = None          # symmetric scratch of the LR exchange kernel (models/lr.py), lazily
 
     # ---- views -------------------------------------------------------------------------
     def clock_view(self) -> _lib.ClockView:
@@ -206,6 +209,8 @@ class DeviceTable:
             self.local_clock = {w: start_clock for w in local_workers}
             self.local_events = {}
             self.fold_clock = start_clock
+            self.write_epoch += 1
+            self.ckpt_barrier = threading.Barrier(max(1, len(self.local_workers)))
 
     def check_error(self):
         if self.hview is not None and int(self.overflow.item()) != 0:
@@ -216,6 +221,9 @@ class DeviceTable:
                                f"(a peer did not reach the expected clock within {self._timeout_s}s)")
 
     def close(self):
+        if self.xchg is not None:
+            self.xchg.close()
+            self.xchg = None
         self.slab.close()
 
     # ---- whole-table helpers (host convenience, not hot path) ----------------------------
@@ -287,6 +295,7 @@ class KVClientTable:
         k32 = keys_as_i32(keys, self.dev)
         v = torch.as_tensor(vals).to(self.dev, dtype=t.dtype, non_blocking=True).contiguous()
         assert v.numel() == k32.numel() * t.k
+        t.write_epoch += 1
         if t.hview is not None:
             _lib.check(self.lib.mps_hash_add(C.byref(t.hview), C.c_void_p(k32.data_ptr()), C.c_void_p(v.data_ptr()),
                                              k32.numel(), C.c_void_p(t.overflow.data_ptr()), self._sp()), "hash_add")
@@ -312,6 +321,7 @@ class KVClientTable:
     def add_all(self, delta: torch.Tensor, zero_src: bool = False):
         t = self.table
         assert delta.is_cuda and delta.dtype == t.dtype and delta.numel() == t.num_keys * t.k
+        t.write_epoch += 1
         _lib.check(self.lib.mps_push_dense(C.byref(t.view), C.c_void_p(delta.data_ptr()), int(zero_src),
                                            t.own_first, self._sp()), "push_dense")
 

@@ -41,17 +41,21 @@ def _resolve(path: str) -> str:
 
 
 def round_to_interval(v: int, interval: int = 100) -> int:
-    return int(round(v / interval)) * interval if interval > 0 else v
+    """Nearest multiple of the checkpoint interval, halves up — the host runtime's RoundToInterval
+    (csrc/core/server.cpp, lround) and the reference's ::round (progress_tracker.hpp:64-85)."""
+    import math
+    return int(math.floor(v / interval + 0.5)) * interval if interval > 0 else v
 
 
 def write_sparse_line(path: str, values: np.ndarray):
     """The VectorStorage::Dump format."""
     idx = np.flatnonzero(values)
+    digits = 17 if values.dtype == np.float64 else 9    # round-trip precision of the table's type
     with open(_resolve(path), "w") as f:
         step = 1 << 18
         for s in range(0, idx.size, step):
             chunk = idx[s:s + step]
-            f.write(" ".join(f"{i}:{values[i]:.9g}" for i in chunk))
+            f.write(" ".join(f"{i}:{values[i]:.{digits}g}" for i in chunk))
             f.write(" ")
 
 
@@ -67,10 +71,30 @@ def read_sparse_line(path: str, size: int, dtype=np.float32) -> np.ndarray:
     return out
 
 
-def dump_table(engine, table, client=None, prefix: Optional[str] = None, interval: int = 100,
+def dump_table(engine, table, client=None, prefix: Optional[str] = None, interval: Optional[int] = None,
                iteration_map: Optional[Dict[int, int]] = None):
-    """Collective, blocking dump of one table: shard values, progress tracker, iteration map."""
+    """Collective, blocking dump of one table: shard values, progress tracker, iteration map.
+
+    Every worker of the task calls it at the same iteration.  With several workers in one process
+    they first meet on a thread barrier (so all their pushes are enqueued), ONE of them runs the
+    process-level protocol (device sync, rank barrier, files, rank barrier) and the others wait for
+    it: rank barriers pair by call order, so they must be issued once per process."""
+    n_local = len(table.local_workers)
+    if n_local > 1:
+        if table.ckpt_barrier.wait() != 0:
+            table.ckpt_barrier.wait()       # the leader is writing; released when it is done
+            return
+    try:
+        _dump_table_once(engine, table, prefix, interval, iteration_map)
+    finally:
+        if n_local > 1:
+            table.ckpt_barrier.wait()
+
+
+def _dump_table_once(engine, table, prefix, interval, iteration_map):
     prefix = prefix if prefix is not None else str(engine.context.get("checkpoint_file_prefix", ""))
+    if interval is None:
+        interval = int(engine.context.get("checkpoint_interval", 100))
     torch.cuda.synchronize(table.device)
     engine.control.barrier()  # every push of every worker has landed
     engine.run_dump_callback()
@@ -112,6 +136,7 @@ def restore_table(engine, table, prefix: Optional[str] = None) -> Dict[int, int]
         vals = read_sparse_line(_paths(prefix, node_id, k, "server_params"), (e - b) * table.k,
                                 np.float32 if table.dtype == torch.float32 else np.float64)
         table.shard_tensor(s).copy_(torch.from_numpy(vals).to(dev))
+        table.write_epoch += 1
         if table.model_type.name == "BSP":
             table.shard_tensor(s, staging=True).zero_()
     clock = 0
