@@ -13,15 +13,27 @@ N_POINTS = 100_000_000
 def run(args, emit):
     import torch.distributed as dist
     from ..parallel.engine import Engine
+
+    engine = Engine.from_env()
+    engine.start_everything(num_server_threads_per_node=max(1, 8 // len(engine.nodes)))
+    rec = measure(engine, args)
+    engine.stop_everything()
+    if engine.node.id == 0:
+        emit(rec)
+    if dist.is_initialized():
+        dist.barrier()
+        dist.destroy_process_group()
+
+
+def measure(engine, args) -> dict:
+    """The k-means benchmark on an already started engine; returns the record (every rank)."""
     from ..parallel.types import MLTask, ModelType, WorkerAlloc
     from ..utils.benchkit import ClockSampler, max_over_ranks, sync_barrier
     from .kmeans import KMeansTrainer, init_random, make_blobs
 
-    engine = Engine.from_env()
     world, rank = len(engine.nodes), engine.node.id
     dev = f"cuda:{engine.device}"
-    servers = max(1, 8 // world)
-    engine.start_everything(num_server_threads_per_node=servers)
+    servers = engine.num_server_threads_per_node
     K, D = K_CLUSTERS, DIM
     n_total = args.samples if args.samples != 10_000_000 else N_POINTS
     n_local = n_total // world
@@ -130,9 +142,6 @@ def run(args, emit):
         rec["e2e"] = {"value": world * B * steps / (res["e2e_ms"] / 1e3), "unit": "samples/s",
                       "h2d_bytes_per_step": B * D * 2, "d2h_bytes_per_step": 4, "steps": steps,
                       "ms_per_step": res["e2e_ms"] / steps, "sse_per_point_last": res["e2e_sse_last"]}
-    engine.stop_everything()
-    if rank == 0:
-        emit(rec)
-    if dist.is_initialized():
-        dist.barrier()
-        dist.destroy_process_group()
+    del x
+    torch.cuda.empty_cache()
+    return rec

@@ -93,6 +93,7 @@ class AsyncBatchLoader:
                     "scratch": torch.empty(batch // 4096 + 4, dtype=torch.int32, device=device),
                 })
         self.bytes_per_batch = 0
+        self.launches_per_batch = 4 if self.packed else 0   # device-side CSR rebuild (scan x3 + unpack)
         self._i = 0
 
     def prefetch(self, row_start: int) -> int:

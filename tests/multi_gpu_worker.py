@@ -12,7 +12,7 @@ import torch
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 sys.path.insert(0, ROOT)
 
-from minips_b200.models.lr import SparseLRTrainer, make_synthetic, oracle_step  # noqa: E402
+from minips_b200.models.lr import CsrBatchSource, SparseLRTrainer, make_synthetic, oracle_step  # noqa: E402
 from minips_b200.parallel.engine import Engine  # noqa: E402
 from minips_b200.parallel.types import MLTask, ModelType, WorkerAlloc  # noqa: E402
 
@@ -66,25 +66,44 @@ def main():
         full = engine.tables[t2].gather_full()
         assert torch.all(full == 20.0 * world), (rank, model, full[:4].tolist())
 
-    # ---- 3. fused LR, dense persistent kernel, BSP: equals synchronous DP SGD
+    # ---- 3. fused LR, dense persistent kernels, BSP: equal synchronous DP SGD.  Both protocols (one exchange
+    #         per step with reduce-at-owner / owner-broadcast, and slab pull / push) and both value types;
+    #         two launches each so the second starts from what the first left in the symmetric scratch.
     nd, rows, batch, alpha, iters = 60_001, 12_000, 4096, 0.05, 5
     datas = [make_synthetic(rows, nd, 40, device=dev, seed=50 + r) for r in range(world)]
     starts = [torch.tensor([(37 * r + 911 * i) % (rows - batch) for i in range(iters)], dtype=torch.int64)
               for r in range(world)]
-    t3 = engine.create_table(num_dims=nd, model_type=ModelType.BSP)
-    out = {}
-
-    def lr_fn(info):
-        tr = SparseLRTrainer(info.create_kv_client_table(t3), datas[rank], alpha)
-        out["loss"] = tr.train_dense(starts[rank].to(dev), batch)
-        out["w"] = tr.client.get_all()
-
-    run_task(engine, [t3], lr_fn)
-    w = torch.zeros(nd, device=dev)
+    w32 = torch.zeros(nd, device=dev)
+    w64 = torch.zeros(nd, device=dev, dtype=torch.float64)
+    d64 = [CsrBatchSource(d.row_ptr, d.col, d.val.double(), d.label.double()) for d in datas]
     for i in range(iters):
-        d = sum(oracle_step(w, datas[r], int(starts[r][i]), batch, alpha)[0] for r in range(world))
-        w = w + d
-    torch.testing.assert_close(out["w"], w, rtol=3e-4, atol=3e-5)
+        w32 = w32 + sum(oracle_step(w32, datas[r], int(starts[r][i]), batch, alpha)[0] for r in range(world))
+        w64 = w64 + sum(oracle_step(w64, d64[r], int(starts[r][i]), batch, alpha)[0] for r in range(world))
+    w = w32
+    multicast = None
+    for dtype, protocol in ((torch.float32, "xchg"), (torch.float64, "xchg"), (torch.float32, "pushpull"),
+                            (torch.float64, "pushpull")):
+        t3 = engine.create_table(num_dims=nd, model_type=ModelType.BSP, dtype=dtype)
+        out = {}
+
+        def lr_fn(info, t3=t3, protocol=protocol):
+            tr = SparseLRTrainer(info.create_kv_client_table(t3), datas[rank], alpha)
+            st = starts[rank].to(dev)
+            tr.train_dense(st[:3], batch, protocol=protocol)
+            tr.train_dense(st[3:], batch, protocol=protocol)
+            out["w"] = tr.client.get_all()
+            if protocol == "xchg":
+                out["replica"] = engine.tables[t3].xchg.replica.clone()
+                out["mc"] = engine.tables[t3].xchg.multicast
+
+        run_task(engine, [t3], lr_fn)
+        if dtype == torch.float64:
+            torch.testing.assert_close(out["w"], w64, rtol=1e-9, atol=1e-12)
+        else:
+            torch.testing.assert_close(out["w"], w32, rtol=3e-4, atol=3e-5)
+        if protocol == "xchg":
+            assert torch.equal(out["replica"], out["w"]), "every rank's replica is the table"
+            multicast = out["mc"]
 
     # ---- 4. fused LR, sparse per-step kernel, BSP
     t4 = engine.create_table(num_dims=nd, model_type=ModelType.BSP)
@@ -204,7 +223,7 @@ def main():
         dist.barrier()
         dist.destroy_process_group()
     if rank == 0:
-        print(f"MULTI_GPU_OK world={world}")
+        print(f"MULTI_GPU_OK world={world} nvls_multicast={multicast}")
 
 
 if __name__ == "__main__":
