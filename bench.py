@@ -137,6 +137,8 @@ def measure_lr(engine, args, data, dtype_name, want_e2e, want_timeline=False):
         result["launches"] = 1 if dense else 2 * K
         if dense and tr.xchg_ok():
             result["nvls"] = bool(engine.tables[tid].xchg.multicast)
+            result["reduce"] = engine.tables[tid].xchg.reduce
+            result["bcast"] = engine.tables[tid].xchg.bcast
         if want_e2e and dense:
             Ke = args.e2e_steps or K
             # the data set lives in pinned host memory in the loader's compact form (u8 row lengths, 24-bit
@@ -172,10 +174,12 @@ def measure_lr(engine, args, data, dtype_name, want_e2e, want_timeline=False):
             tr.train_dense(starts(n_tl).to(dev), B, timeline=tl)
             torch.cuda.synchronize()
             t = tl.view(n_tl, 8).cpu().double()
-            d = ((t[:, 1:6] - t[:, 0:5]) / 1e3)[5:].mean(0).tolist()
-            names = (["gate", "rows+barrier", "clock+owner-wait", "reduce+broadcast", "fold-signal"]
-                     if result["protocol"] == "xchg" else
-                     ["gate", "pull+sync1", "rows+sync2", "pulled-wait", "push+signal"])
+            if result["protocol"] == "xchg":
+                names = ["broadcast-wait", "zero+rows+barrier", "clock+owner-wait", "reduce+broadcast", "signal"]
+                d = ((t[:, 1:6] - t[:, 0:5]) / 1e3)[5:].mean(0).tolist()
+            else:
+                names = ["gate", "pull+sync1", "rows+sync2", "pulled-wait", "push+signal"]
+                d = ((t[:, 1:6] - t[:, 0:5]) / 1e3)[5:].mean(0).tolist()
             if rank == 0:
                 print(f"timeline us ({dtype_name}, {result['protocol']}, rank 0, CTA 0): " +
                       ", ".join(f"{n}={v:.2f}" for n, v in zip(names, d)) +
@@ -223,7 +227,7 @@ def bench_lr_ours(args):
         "precision": val_note,
         "l2_policy": "inputs larger than L2: each step streams a fresh random 21 MB CSR batch of a "
                      f"{n_local * NNZ_PER_ROW * 8 / 1e9:.1f} GB per-GPU dataset; the weight replica is L2-resident by design",
-        "regime": result["regime"], "protocol": result["protocol"], "nvls_multicast": result.get("nvls"),
+        "regime": result["regime"], "protocol": result["protocol"], "nvls_multicast": result.get("nvls"), "owner_reduce": result.get("reduce"), "owner_broadcast": result.get("bcast"),
         "timed_region": (f"median of {len(result['times'])} regions of K steps, each bracketed by barrier + synchronize; "
                          "one persistent cooperative kernel runs the K iterations of a region (device-side clock gating)"
                          if result["regime"] == "dense" else

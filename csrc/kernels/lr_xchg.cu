@@ -4,89 +4,128 @@
 // Reference semantics (server/consistency/bsp_model.cpp:14-43): adds of clock p are buffered and
 // applied only when every worker has clocked; a Get of clock p+1 is answered after that.  The
 // generic device path does it as pull -> compute -> push -> clock with three cross-GPU waits per
-// iteration and the whole table crossing NVLink twice (lr.cu).  Here every rank keeps
+// iteration and the whole table crossing NVLink twice (lr.cu).  Here every rank keeps, in a
+// symmetric buffer that every GPU maps (and, with NVLS, the switch maps as one multicast address),
 //   replica   a full copy of the weights, kept current by the shard owners,
-//   gacc[2]   its own gradient of the running batch (double buffered),
-// in a symmetric buffer that every GPU maps (and, with NVLS, the switch maps as one multicast
-// address).  Iteration p on every rank:
-//   A  gate    folded[s] >= p for every shard (local spin)         = BSP Get gate
-//      zero gacc[(p+1)&1]  (its last readers finished before folded reached p)
-//   B  rows    SpMV + sigmoid + gradient of the batch -> gacc[p&1]        --- grid barrier
-//   C  Clock   progress[worker] = p+1 on every rank (fence.sys first)
+//   gacc[3]   its own gradient of the running batch (triple buffered).
+// Iteration `it` (clock p) on every rank:
+//   A  wait    arrived[o] >= it * G for every owner o: all G CTAs of every owner have finished the
+//              broadcast of clock p (local spin; nothing to wait for in the first iteration)
+//      zero gacc[(p+1)%3]  (last read in owner phase p-2, which every rank finished before it
+//                           published progress p — see D)
+//   B  rows    SpMV + sigmoid + gradient of the batch -> gacc[p%3]            --- grid barrier
+//   C  Clock   progress[worker] = p+1 on every rank (fence.sys, then the flag stores)
 //   D  owner   wait min(progress) >= p+1; for every 16-byte chunk of MY key range:
-//                 sum = multimem.ld_reduce(gacc[p&1])   (the switch adds the 8 GPUs' copies)
+//                 sum = multimem.ld_reduce(gacc[p%3])   (the switch adds the N GPUs' copies)
 //                 w   = weights[chunk] + sum -> weights (the shard itself, master copy)
-//                 multimem.st(replica[chunk], w)        (lands in all 8 replicas)
-//              without NVLS: N peer loads and N peer stores per chunk instead.
-//   E  fold    last CTA out: fence.sys, folded[my shards] = p+1 on every rank
-// One data crossing of |table|/N bytes per direction and GPU with NVLS (the old path: 7/8 of the
-// table each way), two flag waits, one grid barrier.  The flags are the generic tracker's
-// (progress / folded), so generic Get / Add / Clock calls before and after a fused run see a
-// consistent table.
+//                 multimem.st(replica[chunk], w)        (lands in all N replicas)
+//              without NVLS (or where it is slower): N-1 peer loads / N-1 peer stores per chunk.
+//   E  signal  every CTA: bar.sync, fence.sys, arrived[me] += 1 on every rank.  One fence per
+//              CTA, all CTAs in parallel, no second hop through a "last CTA": a reader that sees
+//              the count has synchronised with every CTA's fence through the chain of reds.
+// After the last iteration every rank waits for the last broadcast too and then marks the owners'
+// shards folded at the final clock in its OWN pad, so the generic tracker (Get gate) sees the run.
+// Per iteration: one grid barrier, two cross-GPU waits, two system fences on the critical path,
+// |table|/N bytes in and out per GPU with NVLS plus the (N-1)/N |table| every replica must receive.
 //
 // Requires: BSP, every rank of the table runs exactly one worker through this kernel with the
-// same n_iters, one value per key.
+// same n_iters and the same grid size, one value per key.
 #include "lr_common.cuh"
 
 namespace mps {
 
+// ---------------------------------------------------------------- owner phase
 template <typename T>
-struct XchgPtrs {
-  T* replica;        // local
-  T* gacc;           // local, two buffers `stride` apart
-  T* replica_mc;     // multicast or nullptr
-  T* gacc_mc;
-  int64_t stride;
-};
+__device__ __forceinline__ void bcast_chunk(const MpsClockView& c, const MpsXchg& x, T* rmc, int64_t f,
+                                            const Chunk<T>& w) {
+  if (rmc) {
+    if constexpr (sizeof(T) == 4) {
+      mc_st_chunk(rmc + f, w);
+    } else {  // one 16-byte multicast store (multimem.st has no v2.f64; the payload is just bits)
+      asm volatile("multimem.st.relaxed.sys.global.v4.f32 [%0], {%1,%2,%3,%4};" ::"l"(rmc + f),
+                   "f"(__int_as_float(__double2loint(w.v.x))), "f"(__int_as_float(__double2hiint(w.v.x))),
+                   "f"(__int_as_float(__double2loint(w.v.y))), "f"(__int_as_float(__double2hiint(w.v.y)))
+                   : "memory");
+    }
+    return;
+  }
+  st_chunk(static_cast<T*>(x.replica[c.my_rank]) + f, w);
+  for (int k = 1; k < c.num_ranks; ++k) {
+    int r = c.my_rank + k;
+    if (r >= c.num_ranks) r -= c.num_ranks;
+    st_sys_chunk(static_cast<T*>(x.replica[r]) + f, w);
+  }
+}
 
-// owner phase over flat elements [ob, oe) of the table, chunk-wise
+template <typename T>
+__device__ __forceinline__ void bcast_elem(const MpsClockView& c, const MpsXchg& x, T* rmc, int64_t f, T w) {
+  if (rmc) { mc_st(rmc + f, w); return; }
+  static_cast<T*>(x.replica[c.my_rank])[f] = w;
+  for (int k = 1; k < c.num_ranks; ++k) {
+    int r = c.my_rank + k;
+    if (r >= c.num_ranks) r -= c.num_ranks;
+    st_sys(static_cast<T*>(x.replica[r]) + f, w);
+  }
+}
+
+// flat elements [ob, oe) of the table: reduce the N accumulators, apply, broadcast
 template <typename T>
 __device__ __forceinline__ void owner_reduce_bcast(const MpsTableView& v, const MpsClockView& c, const MpsXchg& x,
-                                                   const XchgPtrs<T>& q, int buf, int64_t ob, int64_t oe,
-                                                   int64_t tid, int64_t nthreads) {
+                                                   int buf, int64_t ob, int64_t oe, int64_t tid, int64_t nthreads) {
   constexpr int N = Chunk<T>::N;
   const int R = c.num_ranks;
-  const int64_t goff = static_cast<int64_t>(buf) * q.stride;
-  const bool aligned = shards_chunk_aligned<T>(v) && (ob % N) == 0;
-  if (aligned) {
+  const int64_t goff = static_cast<int64_t>(buf) * x.gacc_stride;
+  const T* gl = static_cast<const T*>(x.gacc[c.my_rank]) + goff;
+  const T* gmc =
+      (x.gacc_mc && (x.flags & MPS_XCHG_REDUCE_P2P) == 0) ? static_cast<const T*>(x.gacc_mc) + goff : nullptr;
+  T* rmc = (x.replica_mc && (x.flags & MPS_XCHG_BCAST_P2P) == 0) ? static_cast<T*>(x.replica_mc) : nullptr;
+  if (shards_chunk_aligned<T>(v) && (ob % N) == 0) {
     const int64_t nc = (oe - ob) / N;
-    for (int64_t i = tid; i < nc; i += nthreads) {
-      const int64_t f = ob + i * N;
-      Chunk<T> sum;
-      if (q.gacc_mc) {
-        sum = mc_ld_reduce_chunk(q.gacc_mc + goff + f);
+    // two chunks per thread and round: all of a thread's loads are in flight before the first store
+    for (int64_t i = tid; i < nc; i += 2 * nthreads) {
+      const int64_t f0 = ob + i * N, f1 = f0 + nthreads * N;
+      const bool two = i + nthreads < nc;
+      Chunk<T> s0, s1 = Chunk<T>::zero();
+      if (gmc) {
+        s0 = mc_ld_reduce_chunk(gmc + f0);
+        if (two) s1 = mc_ld_reduce_chunk(gmc + f1);
       } else {
-        sum = ld_cg_chunk(q.gacc + goff + f);
+        s0 = ld_cg_chunk(gl + f0);
+        if (two) s1 = ld_cg_chunk(gl + f1);
         for (int k = 1; k < R; ++k) {
           int r = c.my_rank + k;
           if (r >= R) r -= R;
-          sum.add(ld_sys_chunk(static_cast<const T*>(x.gacc[r]) + goff + f));
+          const T* gp = static_cast<const T*>(x.gacc[r]) + goff;
+          const Chunk<T> a = ld_sys_chunk(gp + f0);
+          Chunk<T> b = Chunk<T>::zero();
+          if (two) b = ld_sys_chunk(gp + f1);
+          s0.add(a);
+          s1.add(b);
         }
       }
-      T* wp = shard_elem<T>(v, f);
-      Chunk<T> w;
-      w.v = *reinterpret_cast<const decltype(w.v)*>(wp);
-      w.add(sum);
-      st_chunk(wp, w);
-      if (q.replica_mc) {
-        mc_st_chunk(q.replica_mc + f, w);
-      } else {
-        st_chunk(q.replica + f, w);
-        for (int k = 1; k < R; ++k) {
-          int r = c.my_rank + k;
-          if (r >= R) r -= R;
-          st_sys_chunk(static_cast<T*>(x.replica[r]) + f, w);
-        }
+      T* wp0 = shard_elem<T>(v, f0);
+      Chunk<T> w0;
+      w0.v = *reinterpret_cast<const decltype(w0.v)*>(wp0);
+      w0.add(s0);
+      st_chunk(wp0, w0);
+      bcast_chunk<T>(c, x, rmc, f0, w0);
+      if (two) {
+        T* wp1 = shard_elem<T>(v, f1);
+        Chunk<T> w1;
+        w1.v = *reinterpret_cast<const decltype(w1.v)*>(wp1);
+        w1.add(s1);
+        st_chunk(wp1, w1);
+        bcast_chunk<T>(c, x, rmc, f1, w1);
       }
     }
     ob += nc * N;  // tail below
   }
   for (int64_t f = ob + tid; f < oe; f += nthreads) {
     T sum;
-    if (q.gacc_mc) {
-      sum = mc_ld_reduce(q.gacc_mc + goff + f);
+    if (gmc) {
+      sum = mc_ld_reduce(gmc + f);
     } else {
-      sum = ld_cg(q.gacc + goff + f);
+      sum = ld_cg(gl + f);
       for (int k = 1; k < R; ++k) {
         int r = c.my_rank + k;
         if (r >= R) r -= R;
@@ -96,16 +135,7 @@ __device__ __forceinline__ void owner_reduce_bcast(const MpsTableView& v, const 
     T* wp = shard_elem<T>(v, f);
     const T w = *wp + sum;
     *wp = w;
-    if (q.replica_mc) {
-      mc_st(q.replica_mc + f, w);
-    } else {
-      q.replica[f] = w;
-      for (int k = 1; k < R; ++k) {
-        int r = c.my_rank + k;
-        if (r >= R) r -= R;
-        st_sys(static_cast<T*>(x.replica[r]) + f, w);
-      }
-    }
+    bcast_elem<T>(c, x, rmc, f, w);
   }
 }
 
@@ -137,6 +167,14 @@ __device__ __forceinline__ void replica_fill(const MpsTableView& v, int rot_shar
   }
 }
 
+// every owner's broadcast count reached `target`?  (local spin on this rank's pad)
+__device__ __forceinline__ bool all_arrived(const MpsClockView& c, int target) {
+  const int* a = c.pad[c.my_rank] + MPS_PAD_XARRIVED;
+  for (int r = 0; r < c.num_ranks; ++r)
+    if (ld_acquire_sys(a + r) < target) return false;
+  return true;
+}
+
 template <int L, typename T>
 __global__ void __launch_bounds__(512, 2)
 lr_train_xchg_kernel(const __grid_constant__ MpsTableView v, const __grid_constant__ MpsClockView c,
@@ -149,45 +187,45 @@ lr_train_xchg_kernel(const __grid_constant__ MpsTableView v, const __grid_consta
   const bool multi = c.num_ranks > 1;
   const uint32_t key0 = v.begin[0];
   const uint32_t n_keys = v.begin[v.num_shards] - key0;
+  const int G = static_cast<int>(gridDim.x);
   int* pad = c.pad[c.my_rank];
   GridBarrier grid{pad + MPS_PAD_LOCALCTR + 2, 0};  // zeroed by the host before the launch
   const bool tl = timeline != nullptr && tid == 0;
-  XchgPtrs<T> q;
-  q.replica = static_cast<T*>(x.replica[c.my_rank]);
-  q.gacc = static_cast<T*>(x.gacc[c.my_rank]);
-  q.replica_mc = static_cast<T*>(x.replica_mc);
-  q.gacc_mc = static_cast<T*>(x.gacc_mc);
-  q.stride = x.gacc_stride;
+  T* replica = static_cast<T*>(x.replica[c.my_rank]);
+  T* gacc = static_cast<T*>(x.gacc[c.my_rank]);
   const int64_t ob = c.own_count > 0 ? flat_begin1(v, c.own_first) : 0;
   const int64_t oe = c.own_count > 0 ? flat_begin1(v, c.own_first + c.own_count) : 0;
 
   if (!x.replica_valid) {
     // First launch on this table (or the weights were changed behind the replica's back): wait
-    // for the Get gate of start_clock, copy every shard once, start from clean accumulators.
+    // for the Get gate of start_clock, copy every shard once, start from a clean accumulator.
     if (threadIdx.x == 0) spin_until(c, [&] { return gate_open(c, start_clock); });
     __syncthreads();
-    replica_fill<T>(v, c.own_first, q.replica, tid, nthreads);
-    zero_range(q.gacc + static_cast<int64_t>(start_clock & 1) * q.stride, static_cast<int64_t>(n_keys), tid,
+    replica_fill<T>(v, c.own_first, replica, tid, nthreads);
+    zero_range(gacc + static_cast<int64_t>(start_clock % 3) * x.gacc_stride, static_cast<int64_t>(n_keys), tid,
                nthreads);
     grid.sync();
   }
 
-  for (int it = 0; it < n_iters; ++it) {
+  for (int it = 0; it <= n_iters; ++it) {
     const int p = start_clock + it;
-    const int buf = p & 1;
-    if (tl) timeline[8 * it + 0] = globaltimer_ns();
-    // A. gate: every shard folded up to p (owners have written the weights of clock p into my
-    //    replica and are done reading gacc[buf ^ 1])
-    //    (a timed-out wait raises the pad error flag and every later wait falls through, so a lost
-    //    peer ends the launch with an error on the host instead of a hung GPU)
-    if (threadIdx.x == 0) spin_until(c, [&] { return gate_open(c, p); });
-    __syncthreads();
+    const int buf = p % 3;
+    if (tl && it < n_iters) timeline[8 * it + 0] = globaltimer_ns();
+    // A. every owner's broadcast of this clock has landed (the arrival counts start at zero in
+    //    every launch: the host clears them, and no signal of this launch can precede my first
+    //    Clock).  A timed-out wait raises the pad error flag and every later wait falls through, so
+    //    a lost peer ends the launch with an error on the host instead of a hung GPU.
+    if (it > 0) {
+      if (threadIdx.x == 0) spin_until(c, [&] { return all_arrived(c, it * G); });
+      __syncthreads();
+    }
+    if (it == n_iters) break;
     if (tl) timeline[8 * it + 1] = globaltimer_ns();
-    zero_range(q.gacc + static_cast<int64_t>(buf ^ 1) * q.stride, static_cast<int64_t>(n_keys), tid, nthreads);
+    zero_range(gacc + static_cast<int64_t>((p + 1) % 3) * x.gacc_stride, static_cast<int64_t>(n_keys), tid, nthreads);
     // B. rows
     float loss = 0.f, correct = 0.f;
-    rows_pass<L, true, T>(csr, batch_starts[it], batch, key0, n_keys, q.replica,
-                          q.gacc + static_cast<int64_t>(buf) * q.stride, alpha, multi, tid / L, nthreads / L, loss,
+    rows_pass<L, true, T>(csr, batch_starts[it], batch, key0, n_keys, replica,
+                          gacc + static_cast<int64_t>(buf) * x.gacc_stride, alpha, multi, tid / L, nthreads / L, loss,
                           correct);
     block_accumulate(loss, correct, loss_out + 2 * it);
     grid.sync();
@@ -201,31 +239,30 @@ lr_train_xchg_kernel(const __grid_constant__ MpsTableView v, const __grid_consta
         st_relaxed_sys(c.pad[r] + MPS_PAD_PROGRESS + worker, p + 1);
       }
     }
-    // D. owner phase
-    if (oe > ob) {
-      if (threadIdx.x == 0) spin_until(c, [&] { return pad_min_clock(c) >= p + 1; });
-      __syncthreads();
-      if (tl) timeline[8 * it + 3] = globaltimer_ns();
-      owner_reduce_bcast<T>(v, c, x, q, buf, ob, oe, tid, nthreads);
-      if (tl) timeline[8 * it + 4] = globaltimer_ns();
-      // E. last CTA out publishes folded[s] = p+1.  Every CTA fences its own stores at system
-      //    scope before it arrives; the last one fences again before the flag stores.
-      __syncthreads();
-      if (threadIdx.x == 0) {
-        if (multi) fence_sys(); else __threadfence();
-        const int done = atomicAdd(pad + MPS_PAD_LOCALCTR + 1, 1) + 1;
-        if (done == static_cast<int>(gridDim.x)) {
-          pad[MPS_PAD_LOCALCTR + 1] = 0;
-          if (multi) fence_sys(); else __threadfence();
-          for (int i = 0; i < c.num_ranks; ++i) {
-            const int r = (c.my_rank + i) % c.num_ranks;
-            for (int s = c.own_first; s < c.own_first + c.own_count; ++s)
-              st_relaxed_sys(c.pad[r] + MPS_PAD_FOLDED + s, p + 1);
-          }
-        }
+    // D. owner phase.  Every rank waits here, owner or not: "min(progress) >= p+1" is also what
+    //    makes the accumulator zeroing at the top of the loop safe.
+    if (threadIdx.x == 0) spin_until(c, [&] { return pad_min_clock(c) >= p + 1; });
+    __syncthreads();
+    if (tl) timeline[8 * it + 3] = globaltimer_ns();
+    if (oe > ob) owner_reduce_bcast<T>(v, c, x, buf, ob, oe, tid, nthreads);
+    if (tl) timeline[8 * it + 4] = globaltimer_ns();
+    // E. signal: this CTA's part of the broadcast (and of the shard update) is complete.
+    __syncthreads();
+    if (threadIdx.x == 0) {
+      if (multi) fence_sys(); else __threadfence();
+      for (int i = 0; i < c.num_ranks; ++i) {
+        const int r = (c.my_rank + i) % c.num_ranks;
+        asm volatile("red.relaxed.sys.global.add.s32 [%0], %1;" ::"l"(c.pad[r] + MPS_PAD_XARRIVED + c.my_rank), "r"(1)
+                     : "memory");
       }
     }
     if (tl) timeline[8 * it + 5] = globaltimer_ns();
+  }
+
+  // Every owner's last broadcast (and shard update) has been observed above: mark the shards folded
+  // at the final clock in my own pad — the generic Get gate of later calls reads it there.
+  if (tid == 0) {
+    for (int s = 0; s < c.num_shards; ++s) st_relaxed_sys(pad + MPS_PAD_FOLDED + s, start_clock + n_iters);
   }
 }
 
@@ -257,7 +294,11 @@ static int launch_xchg(const MpsTableView* view, const MpsClockView* clk, int wo
   T alpha = static_cast<T>(alpha_f);
   void* args[] = {&v, &c, &worker, &start_clock, &m, &batch_starts, &n_iters, &batch, &alpha, &x, &loss_out,
                   &timeline};
+  // the in-kernel grid barrier's counter and the broadcast arrival counts start every launch at zero:
+  // all signals of the previous launch were awaited before it ended, none of this launch can precede
+  // this rank's first Clock
   MPS_CHECK(cudaMemsetAsync(c.pad[c.my_rank] + MPS_PAD_LOCALCTR + 2, 0, sizeof(int), st));
+  MPS_CHECK(cudaMemsetAsync(c.pad[c.my_rank] + MPS_PAD_XARRIVED, 0, MPS_MAX_RANKS * sizeof(int), st));
   MPS_CHECK(cudaLaunchCooperativeKernel(fn, dim3(grid), dim3(512), args, 0, st));
   return 0;
 }

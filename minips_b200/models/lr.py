@@ -86,14 +86,15 @@ def make_synthetic(n_rows: int, n_features: int, nnz_per_row: int = 40, device="
 
 class XchgScratch:
     """Symmetric scratch of the reduce-at-owner / owner-broadcasts kernel (csrc/kernels/lr_xchg.cu):
-    per rank one weight replica and two gradient accumulators, mapped by every peer and — when the
+    per rank one weight replica and three gradient accumulators, mapped by every peer and — when the
     fabric has NVLS — by the switch as one multicast address.  Creating it is collective."""
 
     def __init__(self, table: DeviceTable):
+        import os
         from ..parallel.heap import SymmetricBuffer
         n = table.num_keys
         self.stride_bytes = (n * table.itemsize + 255) // 256 * 256
-        self.buf = SymmetricBuffer(3 * self.stride_bytes, table.control, table.device, multicast=True)
+        self.buf = SymmetricBuffer(4 * self.stride_bytes, table.control, table.device, multicast=True)
         x = _lib.Xchg()
         for r in range(table.world):
             x.replica[r] = self.buf.ptrs[r]
@@ -101,8 +102,17 @@ class XchgScratch:
         x.replica_mc = self.buf.mc_ptr or None
         x.gacc_mc = (self.buf.mc_ptr + self.stride_bytes) if self.buf.mc_ptr else None
         x.gacc_stride = self.stride_bytes // table.itemsize
+        # Measured on B200 / NVSwitch: fp64 has only a scalar multimem.ld_reduce, which loses to
+        # 16-byte peer loads on few GPUs; with two GPUs a plain peer store beats the multicast store.
+        how_r = os.environ.get("MINIPS_XCHG_REDUCE", "auto")
+        how_b = os.environ.get("MINIPS_XCHG_BCAST", "auto")
+        p2p_r = how_r == "p2p" or (how_r == "auto" and table.dtype == torch.float64 and table.world < 4)
+        p2p_b = how_b == "p2p" or (how_b == "auto" and table.world <= 2)
+        x.flags = (_lib.XCHG_REDUCE_P2P if p2p_r else 0) | (_lib.XCHG_BCAST_P2P if p2p_b else 0)
         self.c = x
         self.multicast = bool(self.buf.mc_ptr)
+        self.reduce = "p2p" if (p2p_r or not self.multicast) else "multimem"
+        self.bcast = "p2p" if (p2p_b or not self.multicast) else "multimem"
         self.valid_clock = -1       # clock whose weights the local replica holds
         self.valid_epoch = -1       # table.write_epoch at that time
         self.replica = self.buf.local_tensor(0, n, table.dtype)

@@ -20,10 +20,13 @@ PAD_BARRIER = PAD_FOLDED + MAX_SHARDS
 PAD_ERROR = PAD_BARRIER + MAX_RANKS
 PAD_MINCLOCK = PAD_ERROR + 1
 PAD_LOCALCTR = PAD_MINCLOCK + 1
+PAD_XARRIVED = PAD_LOCALCTR + 4
 PAD_INTS = 1024
 
 MODEL_SSP, MODEL_BSP, MODEL_ASP = 0, 1, 2
 F32, F64 = 0, 1
+XCHG_REDUCE_P2P = 1
+XCHG_BCAST_P2P = 2
 
 
 class TableView(C.Structure):
@@ -72,7 +75,7 @@ class Xchg(C.Structure):
         ("gacc_mc", C.c_void_p),
         ("gacc_stride", C.c_int64),
         ("replica_valid", C.c_int32),
-        ("reserved", C.c_int32),
+        ("flags", C.c_int32),
     ]
 
 
