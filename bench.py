@@ -175,7 +175,7 @@ def measure_lr(engine, args, data, dtype_name, want_e2e, want_timeline=False):
             torch.cuda.synchronize()
             t = tl.view(n_tl, 8).cpu().double()
             if result["protocol"] == "xchg":
-                names = ["broadcast-wait", "zero+rows+barrier", "clock+owner-wait", "reduce+broadcast", "signal"]
+                names = ["broadcast-wait", "zero+rows", "clock+owner-wait", "reduce+broadcast", "signal"]
                 d = ((t[:, 1:6] - t[:, 0:5]) / 1e3)[5:].mean(0).tolist()
             else:
                 names = ["gate", "pull+sync1", "rows+sync2", "pulled-wait", "push+signal"]

@@ -8,25 +8,31 @@
 // symmetric buffer that every GPU maps (and, with NVLS, the switch maps as one multicast address),
 //   replica   a full copy of the weights, kept current by the shard owners,
 //   gacc[3]   its own gradient of the running batch (triple buffered).
-// Iteration `it` (clock p) on every rank:
-//   A  wait    arrived[o] >= it * G for every owner o: all G CTAs of every owner have finished the
+// Iteration `it` (clock p) on every rank (G = CTAs per rank, the same on every rank):
+//   A  wait    arrived[o] >= it * G for every owner o: all CTAs of every owner have finished the
 //              broadcast of clock p (local spin; nothing to wait for in the first iteration)
-//      zero gacc[(p+1)%3]  (last read in owner phase p-2, which every rank finished before it
-//                           published progress p — see D)
-//   B  rows    SpMV + sigmoid + gradient of the batch -> gacc[p%3]            --- grid barrier
-//   C  Clock   progress[worker] = p+1 on every rank (fence.sys, then the flag stores)
-//   D  owner   wait min(progress) >= p+1; for every 16-byte chunk of MY key range:
-//                 sum = multimem.ld_reduce(gacc[p%3])   (the switch adds the N GPUs' copies)
+//      zero gacc[(p+1)&1]  (its last readers, the owner phases of clock p-1, are the ones just
+//                           waited for)
+//   B  rows    SpMV + sigmoid + gradient of the batch -> gacc[p&1]
+//   C  Clock   grid barrier, one fence.sys, progress[worker] = p+1 on every rank
+//   D  owner   wait min(progress) >= p+1; for every 16-byte chunk of MY keys:
+//                 sum = multimem.ld_reduce(gacc[p&1])   (the switch adds the N GPUs' copies)
 //                 w   = weights[chunk] + sum -> weights (the shard itself, master copy)
 //                 multimem.st(replica[chunk], w)        (lands in all N replicas)
 //              without NVLS (or where it is slower): N-1 peer loads / N-1 peer stores per chunk.
-//   E  signal  every CTA: bar.sync, fence.sys, arrived[me] += 1 on every rank.  One fence per
-//              CTA, all CTAs in parallel, no second hop through a "last CTA": a reader that sees
-//              the count has synchronised with every CTA's fence through the chain of reds.
-// After the last iteration every rank waits for the last broadcast too and then marks the owners'
-// shards folded at the final clock in its OWN pad, so the generic tracker (Get gate) sees the run.
-// Per iteration: one grid barrier, two cross-GPU waits, two system fences on the critical path,
-// |table|/N bytes in and out per GPU with NVLS plus the (N-1)/N |table| every replica must receive.
+//   E  signal  every CTA: bar.sync, fence.sys, arrived[me] += 1 on every rank.
+// The broadcast has no "last CTA" hop: each CTA publishes its own completion behind its own system
+// fence, all CTAs in parallel, and a reader that sees the full count has synchronised with every
+// CTA's fence through the chain of reds on the counter.  (fence.acq_rel.sys costs 3.3 us on
+// B200 even with nothing outstanding — profiles/nvlink_probe_2gpu.txt — so the protocol is built
+// to have exactly two of them on an iteration's critical path.)
+// After the last iteration every rank has seen every owner's last broadcast and marks, in its OWN
+// pad, every worker clocked and every shard folded at the final clock, so the generic tracker
+// (Get gate, checkpoint) sees the run.
+// The counters live in two sets used by alternate launches; a launch clears the other set for its
+// successor (safe: every signal of the previous launch was consumed before that launch ended).
+// Per iteration and GPU with NVLS: |table|/N bytes in (reduce), |table|/N out (broadcast), plus
+// the (N-1)/N |table| that every replica has to receive.
 //
 // Requires: BSP, every rank of the table runs exactly one worker through this kernel with the
 // same n_iters and the same grid size, one value per key.
@@ -167,12 +173,20 @@ __device__ __forceinline__ void replica_fill(const MpsTableView& v, int rot_shar
   }
 }
 
-// every owner's broadcast count reached `target`?  (local spin on this rank's pad)
-__device__ __forceinline__ bool all_arrived(const MpsClockView& c, int target) {
-  const int* a = c.pad[c.my_rank] + MPS_PAD_XARRIVED;
-  for (int r = 0; r < c.num_ranks; ++r)
-    if (ld_acquire_sys(a + r) < target) return false;
+// all `n` counters at `cnt` reached `target`?  (local spin on this rank's pad)
+__device__ __forceinline__ bool all_reached(const int* cnt, int n, int target) {
+  for (int r = 0; r < n; ++r)
+    if (ld_acquire_sys(cnt + r) < target) return false;
   return true;
+}
+
+// this CTA's part is done: system fence, then +1 on slot `me` of the counter on every rank
+__device__ __forceinline__ void cta_signal(const MpsClockView& c, int slot, bool multi) {
+  if (multi) fence_sys(); else __threadfence();
+  for (int i = 0; i < c.num_ranks; ++i) {
+    const int r = (c.my_rank + i) % c.num_ranks;
+    asm volatile("red.relaxed.sys.global.add.s32 [%0], %1;" ::"l"(c.pad[r] + slot + c.my_rank), "r"(1) : "memory");
+  }
 }
 
 template <int L, typename T>
@@ -189,80 +203,81 @@ lr_train_xchg_kernel(const __grid_constant__ MpsTableView v, const __grid_consta
   const uint32_t n_keys = v.begin[v.num_shards] - key0;
   const int G = static_cast<int>(gridDim.x);
   int* pad = c.pad[c.my_rank];
-  GridBarrier grid{pad + MPS_PAD_LOCALCTR + 2, 0};  // zeroed by the host before the launch
+  const int set = MPS_PAD_XCNT + (x.seq & 1) * 2 * MPS_MAX_RANKS;
+  const int kReady = set, kArrived = set + MPS_MAX_RANKS;
   const bool tl = timeline != nullptr && tid == 0;
   T* replica = static_cast<T*>(x.replica[c.my_rank]);
   T* gacc = static_cast<T*>(x.gacc[c.my_rank]);
   const int64_t ob = c.own_count > 0 ? flat_begin1(v, c.own_first) : 0;
   const int64_t oe = c.own_count > 0 ? flat_begin1(v, c.own_first + c.own_count) : 0;
 
+  GridBarrier grid{pad + MPS_PAD_LOCALCTR + 2, 0};  // zeroed by the host before the launch
   if (!x.replica_valid) {
     // First launch on this table (or the weights were changed behind the replica's back): wait
     // for the Get gate of start_clock, copy every shard once, start from a clean accumulator.
     if (threadIdx.x == 0) spin_until(c, [&] { return gate_open(c, start_clock); });
     __syncthreads();
     replica_fill<T>(v, c.own_first, replica, tid, nthreads);
-    zero_range(gacc + static_cast<int64_t>(start_clock % 3) * x.gacc_stride, static_cast<int64_t>(n_keys), tid,
+    zero_range(gacc + static_cast<int64_t>(start_clock & 1) * x.gacc_stride, static_cast<int64_t>(n_keys), tid,
                nthreads);
     grid.sync();
   }
 
   for (int it = 0; it <= n_iters; ++it) {
     const int p = start_clock + it;
-    const int buf = p % 3;
+    const int buf = p & 1;
     if (tl && it < n_iters) timeline[8 * it + 0] = globaltimer_ns();
-    // A. every owner's broadcast of this clock has landed (the arrival counts start at zero in
-    //    every launch: the host clears them, and no signal of this launch can precede my first
-    //    Clock).  A timed-out wait raises the pad error flag and every later wait falls through, so
-    //    a lost peer ends the launch with an error on the host instead of a hung GPU.
+    // A. every owner's broadcast of this clock has landed.  A timed-out wait raises the pad error
+    //    flag and every later wait falls through, so a lost peer ends the launch with an error on
+    //    the host instead of a hung GPU.
     if (it > 0) {
-      if (threadIdx.x == 0) spin_until(c, [&] { return all_arrived(c, it * G); });
+      if (threadIdx.x == 0) spin_until(c, [&] { return all_reached(pad + kArrived, c.num_ranks, it * G); });
       __syncthreads();
     }
     if (it == n_iters) break;
     if (tl) timeline[8 * it + 1] = globaltimer_ns();
-    zero_range(gacc + static_cast<int64_t>((p + 1) % 3) * x.gacc_stride, static_cast<int64_t>(n_keys), tid, nthreads);
+    zero_range(gacc + static_cast<int64_t>(buf ^ 1) * x.gacc_stride, static_cast<int64_t>(n_keys), tid, nthreads);
     // B. rows
     float loss = 0.f, correct = 0.f;
     rows_pass<L, true, T>(csr, batch_starts[it], batch, key0, n_keys, replica,
                           gacc + static_cast<int64_t>(buf) * x.gacc_stride, alpha, multi, tid / L, nthreads / L, loss,
                           correct);
-    block_accumulate(loss, correct, loss_out + 2 * it);
-    grid.sync();
+    block_accumulate(loss, correct, loss_out + 2 * it);  // ends with bar.sync: the CTA's reds are issued
     if (tl) timeline[8 * it + 2] = globaltimer_ns();
-    // C. Clock: my gradient of clock p is complete.  The grid barrier ordered every CTA's reds
-    //    before this thread; the fence makes them visible system-wide before the flag.
-    if (tid == 0) {
-      if (multi) fence_sys(); else __threadfence();
-      for (int i = 0; i < c.num_ranks; ++i) {
-        const int r = (c.my_rank + i) % c.num_ranks;
-        st_relaxed_sys(c.pad[r] + MPS_PAD_PROGRESS + worker, p + 1);
+    // C + D. Clock, then wait for every rank's gradient.  Across GPUs: one grid barrier, ONE system
+    //        fence by one thread, progress[worker] = p+1 on every rank (per-CTA fences behind the
+    //        rows' reds measured 4 us slower here).  On a single GPU a device-scope fence is all a
+    //        CTA needs, so every CTA counts itself in and the grid barrier is skipped.
+    if (multi) {
+      grid.sync();
+      if (tid == 0) {
+        fence_sys();
+        for (int i = 0; i < c.num_ranks; ++i) {
+          const int r = (c.my_rank + i) % c.num_ranks;
+          st_relaxed_sys(c.pad[r] + MPS_PAD_PROGRESS + worker, p + 1);
+        }
       }
+      if (threadIdx.x == 0) spin_until(c, [&] { return pad_min_clock(c) >= p + 1; });
+    } else if (threadIdx.x == 0) {
+      cta_signal(c, kReady, false);
+      spin_until(c, [&] { return all_reached(pad + kReady, 1, (it + 1) * G); });
     }
-    // D. owner phase.  Every rank waits here, owner or not: "min(progress) >= p+1" is also what
-    //    makes the accumulator zeroing at the top of the loop safe.
-    if (threadIdx.x == 0) spin_until(c, [&] { return pad_min_clock(c) >= p + 1; });
     __syncthreads();
     if (tl) timeline[8 * it + 3] = globaltimer_ns();
     if (oe > ob) owner_reduce_bcast<T>(v, c, x, buf, ob, oe, tid, nthreads);
     if (tl) timeline[8 * it + 4] = globaltimer_ns();
     // E. signal: this CTA's part of the broadcast (and of the shard update) is complete.
     __syncthreads();
-    if (threadIdx.x == 0) {
-      if (multi) fence_sys(); else __threadfence();
-      for (int i = 0; i < c.num_ranks; ++i) {
-        const int r = (c.my_rank + i) % c.num_ranks;
-        asm volatile("red.relaxed.sys.global.add.s32 [%0], %1;" ::"l"(c.pad[r] + MPS_PAD_XARRIVED + c.my_rank), "r"(1)
-                     : "memory");
-      }
-    }
+    if (threadIdx.x == 0) cta_signal(c, kArrived, multi);
     if (tl) timeline[8 * it + 5] = globaltimer_ns();
   }
 
-  // Every owner's last broadcast (and shard update) has been observed above: mark the shards folded
-  // at the final clock in my own pad — the generic Get gate of later calls reads it there.
+  // Every rank's last gradient and every owner's last broadcast / shard update have been observed
+  // above: record that in my own pad for the generic tracker.
   if (tid == 0) {
-    for (int s = 0; s < c.num_shards; ++s) st_relaxed_sys(pad + MPS_PAD_FOLDED + s, start_clock + n_iters);
+    const int fin = start_clock + n_iters;
+    for (int w = 0; w < c.num_workers; ++w) st_relaxed_sys(pad + MPS_PAD_PROGRESS + w, fin);
+    for (int s = 0; s < c.num_shards; ++s) st_relaxed_sys(pad + MPS_PAD_FOLDED + s, fin);
   }
 }
 
@@ -294,11 +309,12 @@ static int launch_xchg(const MpsTableView* view, const MpsClockView* clk, int wo
   T alpha = static_cast<T>(alpha_f);
   void* args[] = {&v, &c, &worker, &start_clock, &m, &batch_starts, &n_iters, &batch, &alpha, &x, &loss_out,
                   &timeline};
-  // the in-kernel grid barrier's counter and the broadcast arrival counts start every launch at zero:
-  // all signals of the previous launch were awaited before it ended, none of this launch can precede
-  // this rank's first Clock
+  // the grid barrier's counter (first-launch path) starts at zero; the counter set of the NEXT launch is
+  // cleared now — all its signals from two launches ago were consumed before that launch ended, and none
+  // of the next launch can be sent before this one has finished on every rank
   MPS_CHECK(cudaMemsetAsync(c.pad[c.my_rank] + MPS_PAD_LOCALCTR + 2, 0, sizeof(int), st));
-  MPS_CHECK(cudaMemsetAsync(c.pad[c.my_rank] + MPS_PAD_XARRIVED, 0, MPS_MAX_RANKS * sizeof(int), st));
+  MPS_CHECK(cudaMemsetAsync(c.pad[c.my_rank] + MPS_PAD_XCNT + ((x.seq + 1) & 1) * 2 * MPS_MAX_RANKS, 0,
+                            2 * MPS_MAX_RANKS * sizeof(int), st));
   MPS_CHECK(cudaLaunchCooperativeKernel(fn, dim3(grid), dim3(512), args, 0, st));
   return 0;
 }

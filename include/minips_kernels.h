@@ -31,7 +31,7 @@ extern "C" {
 #define MPS_PAD_ERROR (MPS_PAD_BARRIER + MPS_MAX_RANKS)      /* [1] sticky error (timeout) flag   */
 #define MPS_PAD_MINCLOCK (MPS_PAD_ERROR + 1)                 /* [1] last min clock seen (debug)   */
 #define MPS_PAD_LOCALCTR (MPS_PAD_MINCLOCK + 1)              /* [4] local CTA-completion counters */
-#define MPS_PAD_XARRIVED (MPS_PAD_LOCALCTR + 4)               /* [MPS_MAX_RANKS] LR exchange: CTAs of owner r done */
+#define MPS_PAD_XCNT (MPS_PAD_LOCALCTR + 4)                   /* [2 sets][ready|arrived][MPS_MAX_RANKS] LR exchange: CTAs of rank r done */
 #define MPS_PAD_INTS 1024                                    /* pad size in int32 (4 KiB)         */
 
 enum { MPS_MODEL_SSP = 0, MPS_MODEL_BSP = 1, MPS_MODEL_ASP = 2 }; /* driver/engine.hpp:25-27 */
@@ -173,7 +173,7 @@ int mps_lr_train_dense_ex(const MpsTableView* view, const MpsClockView* clk, int
 /* BSP iterations as one exchange per step — reduce at the owner, owner broadcasts
  * (csrc/kernels/lr_xchg.cu; semantics of server/consistency/bsp_model.cpp:14-43: adds of a
  * clock become visible only after every worker clocked).  Every rank keeps a full weight
- * replica and three gradient accumulators in a symmetric buffer; replica[r] / gacc[r] address
+ * replica and two gradient accumulators in a symmetric buffer; replica[r] / gacc[r] address
  * rank r's copies from this device, replica_mc / gacc_mc are the NVLS multicast addresses of
  * the same buffers (NULL: plain peer loads / stores instead of multimem.ld_reduce /
  * multimem.st).  gacc_stride = elements between two of a rank's accumulators.
@@ -185,7 +185,7 @@ int mps_lr_train_dense_ex(const MpsTableView* view, const MpsClockView* clk, int
  * broadcasts with peer stores even when replica_mc is set.
  * Collective: every rank of the table runs exactly one worker through this call with the same
  * n_iters and the same number of CTAs (same GPU model, same max_ctas); BSP tables with one value
- * per key; fp32 or fp64.  timeline slots per iteration: start | broadcast-wait | rows+barrier |
+ * per key; fp32 or fp64.  timeline slots per iteration: start | broadcast-wait | zero+rows |
  * clock+owner-wait | reduce+broadcast | signal. */
 #define MPS_XCHG_REDUCE_P2P 1
 #define MPS_XCHG_BCAST_P2P 2 /* broadcast with N-1 peer stores even when replica_mc is set */
@@ -197,6 +197,8 @@ typedef struct MpsXchg {
   int64_t gacc_stride;
   int32_t replica_valid;
   int32_t flags;
+  int32_t seq;      /* number of exchange launches on this table so far (the same on every rank) */
+  int32_t reserved;
 } MpsXchg;
 int mps_lr_train_xchg(const MpsTableView* view, const MpsClockView* clk, int worker, int start_clock,
                       const MpsCsr* csr, const int64_t* batch_starts, int n_iters, int64_t batch,

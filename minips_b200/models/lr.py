@@ -86,7 +86,7 @@ def make_synthetic(n_rows: int, n_features: int, nnz_per_row: int = 40, device="
 
 class XchgScratch:
     """Symmetric scratch of the reduce-at-owner / owner-broadcasts kernel (csrc/kernels/lr_xchg.cu):
-    per rank one weight replica and three gradient accumulators, mapped by every peer and — when the
+    per rank one weight replica and two gradient accumulators, mapped by every peer and — when the
     fabric has NVLS — by the switch as one multicast address.  Creating it is collective."""
 
     def __init__(self, table: DeviceTable):
@@ -94,7 +94,7 @@ class XchgScratch:
         from ..parallel.heap import SymmetricBuffer
         n = table.num_keys
         self.stride_bytes = (n * table.itemsize + 255) // 256 * 256
-        self.buf = SymmetricBuffer(4 * self.stride_bytes, table.control, table.device, multicast=True)
+        self.buf = SymmetricBuffer(3 * self.stride_bytes, table.control, table.device, multicast=True)
         x = _lib.Xchg()
         for r in range(table.world):
             x.replica[r] = self.buf.ptrs[r]
@@ -113,6 +113,7 @@ class XchgScratch:
         self.multicast = bool(self.buf.mc_ptr)
         self.reduce = "p2p" if (p2p_r or not self.multicast) else "multimem"
         self.bcast = "p2p" if (p2p_b or not self.multicast) else "multimem"
+        self.launch_seq = 0         # exchange launches so far (picks the counter set; same on every rank)
         self.valid_clock = -1       # clock whose weights the local replica holds
         self.valid_epoch = -1       # table.write_epoch at that time
         self.replica = self.buf.local_tensor(0, n, table.dtype)
@@ -192,6 +193,8 @@ class SparseLRTrainer:
             assert self.xchg_ok(), "xchg protocol: BSP table with exactly one worker on every rank"
             x = self._xchg()
             x.c.replica_valid = int(x.valid_clock == c.progress and x.valid_epoch == t.write_epoch)
+            x.c.seq = x.launch_seq
+            x.launch_seq += 1
             _lib.check(self.lib.mps_lr_train_xchg(
                 C.byref(t.view), C.byref(cv), c.worker_id, c.progress, C.byref(csr),
                 C.c_void_p(batch_starts.data_ptr()), n_iters, batch, self.alpha, C.byref(x.c),

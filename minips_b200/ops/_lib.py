@@ -20,7 +20,7 @@ PAD_BARRIER = PAD_FOLDED + MAX_SHARDS
 PAD_ERROR = PAD_BARRIER + MAX_RANKS
 PAD_MINCLOCK = PAD_ERROR + 1
 PAD_LOCALCTR = PAD_MINCLOCK + 1
-PAD_XARRIVED = PAD_LOCALCTR + 4
+PAD_XCNT = PAD_LOCALCTR + 4
 PAD_INTS = 1024
 
 MODEL_SSP, MODEL_BSP, MODEL_ASP = 0, 1, 2
@@ -76,6 +76,8 @@ class Xchg(C.Structure):
         ("gacc_stride", C.c_int64),
         ("replica_valid", C.c_int32),
         ("flags", C.c_int32),
+        ("seq", C.c_int32),
+        ("reserved", C.c_int32),
     ]
 
 
