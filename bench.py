@@ -145,8 +145,11 @@ def measure_lr(engine, args, data, dtype_name, want_e2e, want_timeline=False):
             # feature ids, fp32 values, u8 labels; lossless) when it qualifies, else as plain CSR
             host_csr = data.to("cpu")
             packed = PackedCsrHost.from_csr(host_csr)
-            loader = AsyncBatchLoader(packed if packed is not None else host_csr.pin(), B, dev)
-            result["h2d_format"] = (f"packed: u8 row_len + u{packed.id_bits} col + f32 val + u8 label"
+            loader = AsyncBatchLoader(packed if packed is not None else host_csr.pin(), B, dev, depth=3,
+                                      in_place=tr.xchg_ok())
+            result["h2d_format"] = (f"packed: u8 row_len + u{packed.id_bits} col + f32 val + u8 label" +
+                                    (" + i64 offset per 8 rows, read in place by the training kernel"
+                                     if loader.in_place else ", rebuilt into CSR on the device")
                                     if packed is not None else "csr")
             tr.train_stream(loader, starts(W).tolist())      # warm-up
             etimes, hl = [], None
@@ -234,6 +237,7 @@ def bench_lr_ours(args):
                          f"median of {len(result['times'])} regions of K steps; per step one fused pull+SpMV+gradient+push "
                          "kernel (per-nnz peer ld / red.add) + one clock kernel"),
         "repeats_ms": result["times"], "loss_last": result["loss_last"],
+        "host_numa": engine.numa,
     }
     rec = base_record(args, world, "sparse_lr_samples_per_sec", result["value"], "samples/s", ms / K,
                       result["clocks"], cfg, args.dtype, {"gpu_launches": result["launches"] * len(result["times"])})

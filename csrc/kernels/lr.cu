@@ -359,7 +359,7 @@ static int launch_dense_any(const MpsTableView* view, const MpsClockView* clk, i
                             const MpsCsr* csr, const int64_t* batch_starts, int n_iters, int64_t batch,
                             double alpha, void* replica, void* gacc, float* loss_out,
                             unsigned long long* timeline, int avg_nnz, int max_ctas, cudaStream_t st) {
-  if (view->vals_per_key != 1) return static_cast<int>(cudaErrorInvalidValue);
+  if (view->vals_per_key != 1 || csr->format != MPS_CSR_PLAIN) return static_cast<int>(cudaErrorInvalidValue);
   if (view->dtype == MPS_F64)
     return launch_dense<double>(view, clk, worker, start_clock, csr, batch_starts, n_iters, batch, alpha, replica,
                                 gacc, loss_out, timeline, avg_nnz, max_ctas, st);
@@ -378,7 +378,7 @@ int mps_lr_step_sparse(const MpsTableView* view, const MpsClockView* clk, int wo
                        void* stream) {
   (void)worker;
   if (batch <= 0) return 0;
-  if (view->vals_per_key != 1 || (view->dtype != MPS_F32 && view->dtype != MPS_F64))
+  if (view->vals_per_key != 1 || (view->dtype != MPS_F32 && view->dtype != MPS_F64) || csr->format != MPS_CSR_PLAIN)
     return static_cast<int>(cudaErrorInvalidValue);
   int dev = 0, sms = 148;
   cudaGetDevice(&dev);
@@ -419,6 +419,7 @@ int mps_lr_train_dense_ex(const MpsTableView* view, const MpsClockView* clk, int
 int mps_lr_eval(const void* weights, int dtype, uint32_t key0, uint32_t n_keys, const MpsCsr* csr,
                 int64_t row_begin, int64_t n, float* out, void* stream) {
   if (n <= 0) return 0;
+  if (csr->format != MPS_CSR_PLAIN) return static_cast<int>(cudaErrorInvalidValue);
   int dev = 0, sms = 148;
   cudaGetDevice(&dev);
   cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);

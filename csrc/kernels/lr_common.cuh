@@ -185,19 +185,57 @@ __device__ __forceinline__ void red_local(T* p, T v, bool sys) {
   if (sys) red_sys(p, v); else red_gpu(p, v);
 }
 
-template <int L, bool kTrain, typename T>
+// The two sample layouts a kernel can read (MpsCsr.format): plain CSR arrays, or the compact form
+// the host->device loader ships (u8 row lengths + an offset every 8 rows, bit-packed feature ids, u8
+// labels) decoded on the fly, so an end-to-end step needs no separate unpack pass.
+template <bool kPacked> struct CsrView;
+template <> struct CsrView<false> {
+  const MpsCsr& m;
+  template <int L>
+  __device__ __forceinline__ void row(int64_t ridx, int, unsigned, int64_t& beg, int64_t& end) const {
+    beg = m.row_ptr[ridx];
+    end = m.row_ptr[ridx + 1];
+  }
+  __device__ __forceinline__ uint32_t col(int64_t j) const { return ld_stream(m.col + j); }
+  __device__ __forceinline__ float label(int64_t r) const { return m.label[r]; }
+};
+template <> struct CsrView<true> {
+  const MpsCsr& m;
+  // offset of row ridx = offset of its block of 8 rows + the lengths of the rows before it in the
+  // block, summed by the row's own lanes (L >= 8 lanes per row, all of them call this together)
+  template <int L>
+  __device__ __forceinline__ void row(int64_t ridx, int gl, unsigned mask, int64_t& beg, int64_t& end) const {
+    const int k = static_cast<int>(ridx & 7);
+    int part = (gl < k) ? static_cast<int>(m.row_len[(ridx & ~int64_t(7)) + gl]) : 0;
+#pragma unroll
+    for (int o = L / 2; o > 0; o >>= 1) part += __shfl_xor_sync(mask, part, o);
+    beg = m.coarse[ridx >> 3] + part;
+    end = beg + m.row_len[ridx];
+  }
+  __device__ __forceinline__ uint32_t col(int64_t j) const {
+    const int64_t bit = m.bit_off + j * m.id_bits;
+    const uint32_t* w = static_cast<const uint32_t*>(m.packed_ids) + (bit >> 5);
+    const uint64_t two = (static_cast<uint64_t>(ld_stream(w + 1)) << 32) | ld_stream(w);
+    return static_cast<uint32_t>(two >> (bit & 31)) & ((1u << m.id_bits) - 1u);
+  }
+  __device__ __forceinline__ float label(int64_t r) const { return static_cast<float>(m.label_u8[r]); }
+};
+
+template <int L, bool kTrain, typename T, bool kPacked = false>
 __device__ __forceinline__ void rows_pass(const MpsCsr& csr, int64_t row0, int64_t batch, uint32_t key0,
                                           uint32_t n_keys, const T* __restrict__ wloc, T* __restrict__ gacc,
                                           T alpha, bool sys_red, int64_t group, int64_t ngroups, float& loss,
                                           float& correct) {
   constexpr int E = kRowRegs;
+  const CsrView<kPacked> view{csr};
   const int lane = threadIdx.x & 31;
   const int gl = lane & (L - 1);
   const unsigned mask = (L == 32) ? 0xffffffffu : (((1u << L) - 1u) << (lane & ~(L - 1)));
   for (int64_t r = group; r < batch; r += ngroups) {
     int64_t ridx = row0 + r;
     if (ridx >= csr.n_rows) ridx %= csr.n_rows;
-    const int64_t beg = csr.row_ptr[ridx], end = csr.row_ptr[ridx + 1];
+    int64_t beg, end;
+    view.template row<L>(ridx, gl, mask, beg, end);
     uint32_t c[E];
     T x[E];
 #pragma unroll
@@ -206,7 +244,7 @@ __device__ __forceinline__ void rows_pass(const MpsCsr& csr, int64_t row0, int64
       c[e] = 0xffffffffu;
       x[e] = T(0);
       if (j < end) {
-        c[e] = ld_stream(csr.col + j) - key0;
+        c[e] = view.col(j) - key0;
         x[e] = static_cast<T>(ld_stream(csr.val + j));
         if (c[e] >= n_keys) x[e] = T(0);
       }
@@ -218,11 +256,11 @@ __device__ __forceinline__ void rows_pass(const MpsCsr& csr, int64_t row0, int64
 #pragma unroll
     for (int e = 0; e < E; ++e) acc = fma(w[e], x[e], acc);
     for (int64_t j = beg + gl + E * L; j < end; j += L) {  // rows longer than L*E non-zeros
-      const uint32_t cj = ld_stream(csr.col + j) - key0;
+      const uint32_t cj = view.col(j) - key0;
       if (cj < n_keys) acc = fma(ld_cg(wloc + cj), static_cast<T>(ld_stream(csr.val + j)), acc);
     }
     const T z = group_sum<L>(acc, mask);
-    const T y = static_cast<T>(csr.label[ridx]);
+    const T y = static_cast<T>(view.label(ridx));
     const T pred = sigmoid_t(z);
     if (gl == 0) {
       loss += static_cast<float>(logloss_t(z, y));
@@ -235,7 +273,7 @@ __device__ __forceinline__ void rows_pass(const MpsCsr& csr, int64_t row0, int64
         if (x[e] != T(0)) red_local(gacc + c[e], g * x[e], sys_red);
       for (int64_t j = beg + gl + E * L; j < end; j += L) {
         const T kx = static_cast<T>(ld_stream(csr.val + j));
-        const uint32_t cj = ld_stream(csr.col + j) - key0;
+        const uint32_t cj = view.col(j) - key0;
         if (kx != T(0) && cj < n_keys) red_local(gacc + cj, g * kx, sys_red);
       }
     }

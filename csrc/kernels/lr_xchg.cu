@@ -189,7 +189,7 @@ __device__ __forceinline__ void cta_signal(const MpsClockView& c, int slot, bool
   }
 }
 
-template <int L, typename T>
+template <int L, typename T, bool kPacked>
 __global__ void __launch_bounds__(512, 2)
 lr_train_xchg_kernel(const __grid_constant__ MpsTableView v, const __grid_constant__ MpsClockView c,
                      int worker, int start_clock, const __grid_constant__ MpsCsr csr,
@@ -239,7 +239,7 @@ lr_train_xchg_kernel(const __grid_constant__ MpsTableView v, const __grid_consta
     zero_range(gacc + static_cast<int64_t>(buf ^ 1) * x.gacc_stride, static_cast<int64_t>(n_keys), tid, nthreads);
     // B. rows
     float loss = 0.f, correct = 0.f;
-    rows_pass<L, true, T>(csr, batch_starts[it], batch, key0, n_keys, replica,
+    rows_pass<L, true, T, kPacked>(csr, batch_starts[it], batch, key0, n_keys, replica,
                           gacc + static_cast<int64_t>(buf) * x.gacc_stride, alpha, multi, tid / L, nthreads / L, loss,
                           correct);
     block_accumulate(loss, correct, loss_out + 2 * it);  // ends with bar.sync: the CTA's reds are issued
@@ -281,11 +281,11 @@ lr_train_xchg_kernel(const __grid_constant__ MpsTableView v, const __grid_consta
   }
 }
 
-template <typename T>
+template <typename T, bool kPacked>
 static void* xchg_kernel_for(int L) {
-  return L == 8 ? reinterpret_cast<void*>(lr_train_xchg_kernel<8, T>)
-                : (L == 16 ? reinterpret_cast<void*>(lr_train_xchg_kernel<16, T>)
-                           : reinterpret_cast<void*>(lr_train_xchg_kernel<32, T>));
+  return L == 8 ? reinterpret_cast<void*>(lr_train_xchg_kernel<8, T, kPacked>)
+                : (L == 16 ? reinterpret_cast<void*>(lr_train_xchg_kernel<16, T, kPacked>)
+                           : reinterpret_cast<void*>(lr_train_xchg_kernel<32, T, kPacked>));
 }
 
 template <typename T>
@@ -297,7 +297,7 @@ static int launch_xchg(const MpsTableView* view, const MpsClockView* clk, int wo
   cudaGetDevice(&dev);
   cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
   const int L = lanes_for(avg_nnz > 0 ? avg_nnz : 40);
-  void* fn = xchg_kernel_for<T>(L);
+  void* fn = csr->format == MPS_CSR_PACKED ? xchg_kernel_for<T, true>(L) : xchg_kernel_for<T, false>(L);
   MPS_CHECK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, fn, 512, 0));
   if (per_sm < 1) return static_cast<int>(cudaErrorLaunchOutOfResources);
   int grid = sms * per_sm;

@@ -131,7 +131,21 @@ typedef struct MpsCsr {
   const float* val;       /* [nnz] */
   const float* label;     /* [n_rows] in {0,1} (lr_example.cpp:296-297 maps y<0 to 0) */
   int64_t n_rows;
+  /* format = MPS_CSR_PACKED: the loader's compact host->device layout, read in place by
+   * mps_lr_train_xchg (every other entry point wants MPS_CSR_PLAIN, the zero default):
+   * row_len [n_rows] u8; coarse [n_rows/8 + 1] = offset (in non-zeros) of rows 0, 8, 16, ...;
+   * packed_ids = little-endian bit stream, 4-byte aligned with a word of slack, id_bits bits
+   * per feature id, the first one at bit bit_off; label_u8 [n_rows]; val as above. */
+  int32_t format;
+  int32_t id_bits;
+  int32_t bit_off;
+  int32_t reserved;
+  const uint8_t* row_len;
+  const int64_t* coarse;
+  const void* packed_ids;
+  const uint8_t* label_u8;
 } MpsCsr;
+enum { MPS_CSR_PLAIN = 0, MPS_CSR_PACKED = 1 };
 
 /* One LR iteration, sparse regime: Get + forward SpMV + sigmoid + gradient + Add in ONE
  * kernel (lr_example.cpp:260,293-313): each warp walks a CSR row, loads the row's weights

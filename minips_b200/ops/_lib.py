@@ -25,6 +25,7 @@ PAD_INTS = 1024
 
 MODEL_SSP, MODEL_BSP, MODEL_ASP = 0, 1, 2
 F32, F64 = 0, 1
+CSR_PLAIN, CSR_PACKED = 0, 1
 XCHG_REDUCE_P2P = 1
 XCHG_BCAST_P2P = 2
 
@@ -63,6 +64,14 @@ class Csr(C.Structure):
         ("val", C.c_void_p),
         ("label", C.c_void_p),
         ("n_rows", C.c_int64),
+        ("format", C.c_int32),      # CSR_PLAIN / CSR_PACKED
+        ("id_bits", C.c_int32),
+        ("bit_off", C.c_int32),
+        ("reserved", C.c_int32),
+        ("row_len", C.c_void_p),
+        ("coarse", C.c_void_p),
+        ("packed_ids", C.c_void_p),
+        ("label_u8", C.c_void_p),
     ]
 
 

@@ -68,6 +68,7 @@ class Engine:
         self.context: Dict[str, object] = {}
         self.iteration_map: Dict[int, int] = {}
         self.started = False
+        self.numa = None
 
     # ---- lifecycle (engine.cpp:17-44) -------------------------------------------------------
     def start_everything(self, num_server_threads_per_node: int = 1):
@@ -289,12 +290,17 @@ class Engine:
         local_rank = int(os.environ.get("LOCAL_RANK", "0"))
         if device is None:
             device = local_rank
+        numa = None
         if torch.cuda.is_available():
             torch.cuda.set_device(device)
+            from ..utils.numa import bind_to_gpu_node
+            numa = bind_to_gpu_node(device)
         if world > 1 and not dist.is_initialized():
             os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
             os.environ.setdefault("MASTER_PORT", "29511")
             dist.init_process_group(backend="nccl" if torch.cuda.is_available() else "gloo",
                                     rank=rank, world_size=world)
         nodes = [Node(i, "localhost", 0) for i in range(world)]
-        return cls(nodes[rank], nodes, device=device)
+        eng = cls(nodes[rank], nodes, device=device)
+        eng.numa = numa
+        return eng

@@ -61,13 +61,22 @@ class PackedCsrHost:
 
 
 class AsyncBatchLoader:
-    def __init__(self, host, batch: int, device, depth: int = 2):
+    """depth staged batches on the device, filled by a copy stream from pinned host memory.
+
+    in_place=True (packed host data only): the training kernel reads the compact form directly
+    (csrc/kernels/lr_common.cuh CsrView<true>), so a step needs no device-side rebuild — the loader
+    ships, besides the packed arrays, the nnz offset of every 8th row of the batch (64 KiB), which it
+    cuts out of the host row_ptr."""
+
+    def __init__(self, host, batch: int, device, depth: int = 2, in_place: bool = False):
         self.packed = isinstance(host, PackedCsrHost)
         if self.packed:
             assert host.row_len.is_pinned() and host.ids.is_pinned() and host.val.is_pinned() and host.label_u8.is_pinned()
         else:
             assert host.row_ptr.is_pinned() and host.col.is_pinned() and host.val.is_pinned() and host.label.is_pinned()
         self.host = host
+        self.in_place = bool(in_place) and self.packed
+        assert not self.in_place or batch % 8 == 0
         self.batch = batch
         self.device = device
         self.depth = depth
@@ -92,8 +101,15 @@ class AsyncBatchLoader:
                     "label_u8": torch.empty(batch, dtype=torch.uint8, device=device),
                     "scratch": torch.empty(batch // 4096 + 4, dtype=torch.int32, device=device),
                 })
+                if self.in_place:
+                    self.slots[-1].update({
+                        "coarse": torch.empty(batch // 8 + 1, dtype=torch.int64, device=device),
+                        "coarse_host": torch.empty(batch // 8 + 1, dtype=torch.int64).pin_memory(),
+                        "copied": None,
+                    })
         self.bytes_per_batch = 0
-        self.launches_per_batch = 4 if self.packed else 0   # device-side CSR rebuild (scan x3 + unpack)
+        # device-side CSR rebuild (scan x3 + unpack) unless the kernel reads the packed form itself
+        self.launches_per_batch = 4 if (self.packed and not self.in_place) else 0
         self._i = 0
 
     def prefetch(self, row_start: int) -> int:
@@ -116,6 +132,13 @@ class AsyncBatchLoader:
                 slot["id_bytes"] = byte1 - byte0
                 slot["val"][:e - b].copy_(h.val[b:e], non_blocking=True)
                 slot["label_u8"].copy_(h.label_u8[row_start:row_start + B], non_blocking=True)
+                if self.in_place:
+                    if slot["copied"] is not None:
+                        slot["copied"].synchronize()      # the previous copy out of this pinned staging area
+                    torch.sub(h.row_ptr[row_start:row_start + B + 1:8], b, out=slot["coarse_host"])
+                    slot["coarse"].copy_(slot["coarse_host"], non_blocking=True)
+                    slot["copied"] = torch.cuda.Event()
+                    slot["copied"].record(self.copy_stream)
             else:
                 slot["row_ptr"].copy_(h.row_ptr[row_start:row_start + B + 1], non_blocking=True)
                 slot["col"][:e - b].copy_(h.col[b:e], non_blocking=True)
@@ -124,8 +147,8 @@ class AsyncBatchLoader:
             slot["ready"].record(self.copy_stream)
         slot["base"] = 0 if self.packed else b
         slot["nnz"] = e - b
-        self.bytes_per_batch = (B + slot["id_bytes"] + 4 * (e - b) + B) if self.packed else \
-            ((B + 1) * 8 + (e - b) * 8 + B * 4)
+        self.bytes_per_batch = (B + slot["id_bytes"] + 4 * (e - b) + B + (8 * (B // 8 + 1) if self.in_place else 0)) \
+            if self.packed else ((B + 1) * 8 + (e - b) * 8 + B * 4)
         return k
 
     def acquire(self, k: int, stream: Optional[torch.cuda.Stream] = None) -> CsrBatchSource:
@@ -135,7 +158,7 @@ class AsyncBatchLoader:
         slot = self.slots[k]
         st = stream or torch.cuda.current_stream()
         st.wait_event(slot["ready"])
-        if self.packed:
+        if self.packed and not self.in_place:
             # rebuild row_ptr / col / label on the compute stream (three small scan launches + one unpack)
             import ctypes as C
             from ..ops import _lib
@@ -157,6 +180,14 @@ class AsyncBatchLoader:
         m.val = slot["val"].data_ptr() - 4 * slot["base"]
         m.label = slot["label"].data_ptr()
         m.n_rows = self.batch
+        if self.in_place:
+            m.format = _lib.CSR_PACKED
+            m.id_bits = self.host.id_bits
+            m.bit_off = slot["bit_off"]
+            m.row_len = slot["row_len"].data_ptr()
+            m.coarse = slot["coarse"].data_ptr()
+            m.packed_ids = slot["ids"].data_ptr()
+            m.label_u8 = slot["label_u8"].data_ptr()
         return m
 
     def release(self, k: int, stream: Optional[torch.cuda.Stream] = None):

@@ -218,3 +218,47 @@ def test_long_rows(engine):
     w_ref, _ = _oracle(data, num_dims, [0, 0], batch, alpha)
     torch.testing.assert_close(out["dense"], w_ref, rtol=3e-4, atol=3e-5)
     torch.testing.assert_close(out["sparse"], w_ref, rtol=3e-4, atol=3e-5)
+
+
+@pytest.mark.parametrize("dtype", [torch.float32, torch.float64])
+def test_stream_reads_packed_batches_in_place(engine, dtype):
+    """End-to-end steps: batches arrive from pinned host memory in the loader's compact form and the
+    training kernel decodes them itself (row offsets from the per-8-rows table, bit-packed ids, u8
+    labels) — one launch per step.  Same result as the plain-CSR oracle."""
+    from minips_b200.models.lr import SparseLRTrainer, make_synthetic
+    from minips_b200.utils.loader import AsyncBatchLoader, PackedCsrHost
+    num_dims, n_rows, batch, alpha = 70_001, 9000, 2048, 0.05
+    g = torch.Generator(device="cuda").manual_seed(5)
+    # ragged rows (0..60 non-zeros) so that the offset arithmetic is exercised
+    lens = torch.randint(0, 61, (n_rows,), device="cuda", generator=g)
+    rp = torch.zeros(n_rows + 1, dtype=torch.int64, device="cuda")
+    rp[1:] = torch.cumsum(lens, 0)
+    nnz = int(rp[-1])
+    from minips_b200.models.lr import CsrBatchSource
+    col = torch.randint(0, num_dims, (nnz,), device="cuda", generator=g, dtype=torch.int64).to(torch.int32)
+    val = torch.randn(nnz, device="cuda", generator=g)
+    lab = (torch.rand(n_rows, device="cuda", generator=g) < 0.5).float()
+    data = CsrBatchSource(rp, col, val, lab)
+    tid = engine.create_table(num_dims=num_dims, model_type=ModelType.BSP, dtype=dtype)
+    starts = [0, 3001, 6951]
+    out = {}
+
+    def fn(info):
+        tr = SparseLRTrainer(info.create_kv_client_table(tid), data, alpha)
+        packed = PackedCsrHost.from_csr(data.to("cpu"))
+        assert packed is not None and packed.id_bits == 20
+        loader = AsyncBatchLoader(packed, batch, "cuda", depth=2, in_place=True)
+        assert loader.in_place and loader.launches_per_batch == 0
+        out["loss"] = tr.train_stream(loader, starts)
+        torch.cuda.synchronize()
+        out["w"] = tr.client.get_all()
+
+    _run(engine, tid, fn)
+    if dtype == torch.float64:
+        w_ref, stats = _oracle64(data, num_dims, starts, batch, alpha)
+        torch.testing.assert_close(out["w"], w_ref, rtol=1e-9, atol=1e-12)
+    else:
+        w_ref, stats = _oracle(data, num_dims, starts, batch, alpha)
+        torch.testing.assert_close(out["w"], w_ref, rtol=2e-4, atol=2e-5)
+    for i, (l, c) in enumerate(stats):
+        assert abs(out["loss"][i, 0].item() - l) <= 2e-3 * abs(l) + 1e-2
