@@ -32,8 +32,10 @@ def main():
     os.makedirs(os.path.join(OUT, "obj"), exist_ok=True)
     os.makedirs(os.path.join(OUT, "bin"), exist_ok=True)
     libzmq, libdir = find_libzmq()
-    flags = ["-std=c++11", os.environ.get("MINIPS_REF_OPT", "-O2"), "-w", "-pthread", "-DHAS_HADOOP", "-include", "cstdint", "-include", "cstring", "-include", "string",
-             "-include", "functional", "-include", "memory", "-include", "algorithm", "-include", "fcntl.h", f"-I{os.path.join(HERE, 'shims')}", f"-I{REF}"]
+    flags = ["-std=c++11", os.environ.get("MINIPS_REF_OPT", "-O2"), "-w", "-pthread", "-DHAS_HADOOP", "-include",
+        "cstdint", "-include", "cstring", "-include", "string",
+             "-include", "functional", "-include", "memory", "-include", "algorithm", "-include", "fcntl.h",
+             f"-I{os.path.join(HERE, 'shims')}", f"-I{REF}"]
     dirs = ["base", "comm", "driver", "server", "worker", "master", "io"]
     srcs, tests = [], []
     for d in dirs:

@@ -1,7 +1,8 @@
 // Push/pull microbenchmark ON the reference (our own program against the unmodified MiniPs library):
 // the baseline of BASELINE.json config 5 ("keys/s and GB/s vs batch size ... against the reference ZMQ
 // build").  One process per node (config file like the reference's), one worker and one server thread per
-// node, a double table (the reference's KVPairs is fixed to double) range-partitioned evenly over the nodes, ASP so nothing gates.
+// node, a double table (the reference's KVPairs is fixed to double) range-partitioned evenly over the nodes, ASP so
+// nothing gates.
 //
 // For each batch size n the worker times, with std::chrono around the reference's own calls,
 //   push: Add(keys, vals) + Clock()  followed by a Get of one key per shard (Add is fire-and-forget in the
@@ -111,7 +112,8 @@ int main(int argc, char** argv) {
             pull_ms.push_back(tg);
           }
         }
-        std::printf("RESULT node=%u mode=%s n=%d push_ms=%.4f pull_ms=%.4f\n", me.id, mode == 0 ? "spread" : "contig", n,
+        std::printf("RESULT node=%u mode=%s n=%d push_ms=%.4f pull_ms=%.4f\n", me.id, mode == 0 ? "spread"
+            : "contig", n,
                     median(push_ms), median(pull_ms));
         std::fflush(stdout);
       }

@@ -55,6 +55,8 @@ class string_ref {
 };
 inline bool operator==(string_ref a, string_ref b) { return a.size() == b.size() && a.compare(b) == 0; }
 inline bool operator!=(string_ref a, string_ref b) { return !(a == b); }
-inline std::ostream& operator<<(std::ostream& os, string_ref s) { return os.write(s.data(), static_cast<std::streamsize>(s.size())); }
+inline std::ostream& operator<<(std::ostream& os, string_ref s) {
+  return os.write(s.data(), static_cast<std::streamsize>(s.size()));
+}
 }  // namespace boost
 #endif

@@ -27,7 +27,9 @@ inline std::map<std::string, FlagEntry>& Registry() {
   static std::map<std::string, FlagEntry> r;
   return r;
 }
-inline bool ParseBool(const std::string& v) { return v == "true" || v == "True" || v == "1" || v == "t" || v == "yes" || v.empty(); }
+inline bool ParseBool(const std::string& v) {
+  return v == "true" || v == "True" || v == "1" || v == "t" || v == "yes" || v.empty();
+}
 struct Registrar {
   Registrar(const char* name, const char* type, const char* help, bool* p, bool d) {
     Registry()[name] = {name, type, help, d ? "true" : "false", [p](const std::string& v) { *p = ParseBool(v); },

@@ -200,17 +200,21 @@ def run_lr(args, ref_bin):
         except OSError:
             pass
         return {"impl": "reference",
-                "unavailable": f"reference run failed (exit codes {rcs}, {len(times)}/{n * wpn} worker timings): {tail}"}
+                "unavailable": (f"reference run failed (exit codes {rcs}, {len(times)}/{n * wpn} worker timings): "
+                                f"{tail}")}
     total_ms = max(times)
     ms_per_step = total_ms / (steps + warm)
     value = global_batch / (ms_per_step / 1e3)
     return {
         "metric": "sparse_lr_samples_per_sec", "value": value, "unit": "samples/s", "n_gpus": n_gpus,
-        "steps": steps, "steps_requested": args.steps, "warmup": warm, "ms_per_step": ms_per_step, "higher_is_better": True,
-        "scaling": "weak", "vs_baseline": None, "dtype": "fp64 parameters (reference KVClientTable<double>), fp32 features",
+        "steps": steps, "steps_requested": args.steps, "warmup": warm, "ms_per_step": ms_per_step,
+        "higher_is_better": True,
+        "scaling": "weak", "vs_baseline": None,
+        "dtype": "fp64 parameters (reference KVClientTable<double>), fp32 features",
         "data": "synthetic", "impl": "reference",
         "config": {
-            "model": "sparse_logistic_regression", "samples": rows, "samples_requested": rows_requested, "features": features, "nnz_per_row": NNZ_PER_ROW,
+            "model": "sparse_logistic_regression", "samples": rows, "samples_requested": rows_requested,
+            "features": features, "nnz_per_row": NNZ_PER_ROW,
             "server_shards": servers * n, "consistency": args.model, "staleness": args.staleness,
             "global_batch": global_batch, "seq_len": None,
             "parallelism": f"{n} reference node processes on this box x ({wpn} worker + {servers} server thread(s)) "

@@ -21,7 +21,8 @@ def run(args):
             return None
         return {"impl": "reference",
                 "unavailable": "the reference KMeans app cannot run K=1024, d=128: it stores the per-centre counts in "
-                               "params[K][i], a row of num_dims entries (kmeans_helper.hpp:41, needs K <= num_dims), and "
+                               "params[K][i], a row of num_dims entries (kmeans_helper.hpp:41, needs K <= num_dims), "
+                               "and "
                                "its random_init re-seeds rand() with time(NULL) per draw (one centre per second); see "
                                "BASELINE.md section 3"}
     if not os.path.exists(REF_BIN):

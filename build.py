@@ -160,7 +160,10 @@ def main():
     ap.add_argument("--force", action="store_true")
     ap.add_argument("--sass", action="store_true")
     ap.add_argument("--only", choices=["kernels", "core"], default=None)
+    ap.add_argument("--host-only", action="store_true", help="C++ host runtime only (CI boxes without nvcc)")
     a = ap.parse_args()
+    if a.host_only:
+        a.only = "core"
     if a.only in (None, "kernels"):
         build_kernels(a.force)
     if a.only in (None, "core"):

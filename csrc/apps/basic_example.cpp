@@ -29,7 +29,8 @@ int main(int argc, char** argv) {
   const uint64_t n_keys = static_cast<uint64_t>(ctx.get_int32("num_keys"));
   std::vector<Range> ranges;
   const uint64_t per = n_keys / nodes.size();
-  for (size_t i = 0; i < nodes.size(); ++i) ranges.emplace_back(per * i, i + 1 == nodes.size() ? n_keys : per * (i + 1));
+  for (size_t i = 0; i < nodes.size(); ++i) ranges.emplace_back(per * i, i + 1 == nodes.size() ? n_keys
+      : per * (i + 1));
   const uint32_t table = engine.CreateTable<double>(ranges, ModelType::SSP, StorageType::Map, 1);
   engine.Barrier();
 

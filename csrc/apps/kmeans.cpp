@@ -100,7 +100,8 @@ static Centers InitCenters(const std::string& mode, int K, int D, const std::vec
       total += best;
     }
     for (size_t i = 0; i < data.size(); ++i)
-      if (total > 0 && std::uniform_real_distribution<double>(0, 1)(rng) < std::min(1.0, 2.0 * K * d2[i] / total)) cand.push_back(data[i]);
+      if (total > 0 && std::uniform_real_distribution<double>(0, 1)(rng) < std::min(1.0,
+          2.0 * K * d2[i] / total)) cand.push_back(data[i]);
     if (cand.size() > static_cast<size_t>(20 * K)) break;
   }
   while (cand.size() < static_cast<size_t>(K)) cand.push_back(data[pick(rng)]);
@@ -115,11 +116,13 @@ static Centers InitCenters(const std::string& mode, int K, int D, const std::vec
 int main(int argc, char** argv) {
   auto& f = Flags::Get();
   for (auto kv : std::vector<std::pair<const char*, const char*>>{
-           {"my_id", "0"}, {"config_file", ""}, {"input", ""}, {"hdfs_namenode", "localhost"}, {"hdfs_namenode_port", "9000"},
+           {"my_id", "0"}, {"config_file", ""}, {"input", ""}, {"hdfs_namenode", "localhost"}, {"hdfs_namenode_port",
+               "9000"},
            {"assigner_master_port", "19201"}, {"kModelType", "SSP"}, {"kStorageType", "Vector"}, {"num_dims", "123"},
            {"K", "2"}, {"batch_size", "100"}, {"num_iters", "10"}, {"kStaleness", "0"}, {"alpha", "0.1"},
            {"kmeans_init_mode", "random"}, {"report_interval", "2"}, {"report_worker", "0"}, {"report_prefix", ""},
-           {"num_nodes", "0"}, {"num_workers_per_node", "1"}, {"num_servers_per_node", "1"}, {"num_local_load_thread", "2"},
+           {"num_nodes", "0"}, {"num_workers_per_node", "1"}, {"num_servers_per_node",
+               "1"}, {"num_local_load_thread", "2"},
            {"heartbeat_interval", "-1"}, {"block_size", "4194304"}, {"seed", "1"}})
     f.Define(kv.first, kv.second);
   f.Parse(argc, argv);
@@ -130,7 +133,8 @@ int main(int argc, char** argv) {
   MINIPS_CHECK(ctx.get_int32("num_servers_per_node") > 0 && ctx.get_int32("num_servers_per_node") <= 20);
   MINIPS_CHECK(ctx.get_int32("kStaleness") >= 0 && ctx.get_int32("kStaleness") <= 5);
   const std::string mode = ctx.get_string("kmeans_init_mode");
-  MINIPS_CHECK(mode == "random" || mode == "kmeans++" || mode == "kmeans_parallel") << "unknown kmeans_init_mode " << mode;
+  MINIPS_CHECK(mode == "random" || mode == "kmeans++"
+      || mode == "kmeans_parallel") << "unknown kmeans_init_mode " << mode;
   std::vector<Node> nodes = ParseFile(ctx.get_string("config_file"));
   const Node my_node = GetNodeById(nodes, ctx.get_int32("my_id"));
   const int K = ctx.get_int32("K"), D = ctx.get_int32("num_dims");
@@ -157,7 +161,8 @@ int main(int argc, char** argv) {
     for (size_t i = 0; i < shards; ++i) r.emplace_back(n * i / shards, n * (i + 1) / shards);  // never drops keys
     return r;
   };
-  const uint32_t t_c = engine.CreateTable<double>(split(static_cast<uint64_t>(K) * D), model, StorageType::Vector, ctx.get_int32("kStaleness"));
+  const uint32_t t_c = engine.CreateTable<double>(split(static_cast<uint64_t>(K) * D), model, StorageType::Vector,
+      ctx.get_int32("kStaleness"));
   const uint32_t t_n = engine.CreateTable<double>(split(K), model, StorageType::Vector, ctx.get_int32("kStaleness"));
   engine.Barrier();
 
@@ -180,7 +185,8 @@ int main(int argc, char** argv) {
     tc->Clock();
     tn->Clock();
     std::cout << "[init] " << mode << " seeding took "
-              << std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t0).count() << " ms" << std::endl;
+              << std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t0).count() << " ms"
+              << std::endl;
   });
   engine.Run(init);  // collective: nodes without a worker of the task still take part in its barriers
   engine.Barrier();
@@ -205,7 +211,8 @@ int main(int argc, char** argv) {
       tc->Get(keys_c, &pull);
       tn->Get(keys_n, &members);
       Centers cur(K, std::vector<double>(D));
-      for (int k = 0; k < K; ++k) std::copy(pull.begin() + static_cast<size_t>(k) * D, pull.begin() + static_cast<size_t>(k + 1) * D, cur[k].begin());
+      for (int k = 0; k < K; ++k) std::copy(pull.begin() + static_cast<size_t>(k) * D,
+          pull.begin() + static_cast<size_t>(k + 1) * D, cur[k].begin());
       std::vector<double> norms(K), cnt0 = members;
       for (int k = 0; k < K; ++k) norms[k] = Norm2(cur[k]);
       for (int b = 0; b < per_worker; ++b) {
@@ -219,7 +226,8 @@ int main(int argc, char** argv) {
       }
       std::vector<double> delta(keys_c.size()), dn(K);
       for (int k = 0; k < K; ++k)
-        for (int j = 0; j < D; ++j) delta[static_cast<size_t>(k) * D + j] = cur[k][j] - pull[static_cast<size_t>(k) * D + j];
+        for (int j = 0; j < D; ++j)
+          delta[static_cast<size_t>(k) * D + j] = cur[k][j] - pull[static_cast<size_t>(k) * D + j];
       for (int k = 0; k < K; ++k) dn[k] = members[k] - cnt0[k];
       tc->Add(keys_c, delta);
       tc->Clock();
@@ -234,13 +242,15 @@ int main(int argc, char** argv) {
         const double ms = std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t0).count();
         std::cout << "iter " << it + 1 << "\tSSE " << sse << "\t" << ms << " ms" << std::endl;
         if (!ctx.get_string("report_prefix").empty()) {
-          io::ofstream out(ctx.get_string("report_prefix") + "_" + ctx.get_string("my_id"), std::ios_base::out | std::ios_base::app);
+          io::ofstream out(ctx.get_string("report_prefix") + "_" + ctx.get_string("my_id"),
+              std::ios_base::out | std::ios_base::app);
           out << it + 1 << "\t" << sse << "\t" << ms << "\n";
         }
       }
     }
     std::cout << "Total training time: "
-              << std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t0).count() << " ms on worker "
+              << std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t0).count()
+              << " ms on worker "
               << info.worker_id << std::endl;
   });
   engine.Run(task);

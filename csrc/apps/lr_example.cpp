@@ -139,12 +139,14 @@ static int Training(const Node& my_node, const std::vector<Node>& nodes, const N
 
   MLTask task;
   std::vector<WorkerAlloc> alloc;
-  for (const auto& n : engine.GetNodes()) alloc.push_back({n.id, static_cast<uint32_t>(ctx.get_int32("num_workers_per_node"))});
+  for (const auto& n : engine.GetNodes()) alloc.push_back({n.id,
+      static_cast<uint32_t>(ctx.get_int32("num_workers_per_node"))});
   task.SetWorkerAlloc(alloc);
   task.SetTables({table});
   std::mutex print_mu;
   task.SetLambda([&](const Info& info) {
-    lib::BatchDataSampler<SVMItem> sampler(data, batch, static_cast<uint64_t>(ctx.get_int32("seed")) * 1000 + info.worker_id + 1);
+    lib::BatchDataSampler<SVMItem> sampler(data, batch,
+        static_cast<uint64_t>(ctx.get_int32("seed")) * 1000 + info.worker_id + 1);
     // all batches up front, like lr_example.cpp:231-236
     std::vector<SArray<Key>> future_keys;
     std::vector<std::vector<const SVMItem*>> future_ptrs;
@@ -157,7 +159,8 @@ static int Training(const Node& my_node, const std::vector<Node>& nodes, const N
     SArray<double> params, deltas;
     std::mt19937 rng(info.worker_id + 17);
     const auto t0 = std::chrono::steady_clock::now();
-    auto elapsed_ms = [&] { return std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t0).count(); };
+    auto elapsed_ms = [&] { return std::chrono::duration<double,
+        std::milli>(std::chrono::steady_clock::now() - t0).count(); };
     for (int i = Context::get_instance().get_iteration(info.worker_id); i < iters; ++i) {
       const SArray<Key>& keys = future_keys[i];
       if (keys.empty()) {
@@ -202,8 +205,10 @@ static int Training(const Node& my_node, const std::vector<Node>& nodes, const N
         t->CheckPoint();
         MINIPS_LOG(0) << "checkpoint at iteration " << i + 1 << " took " << elapsed_ms() - c0 << " ms";
       }
-      if (report_interval > 0 && (i + 1) % report_interval == 0 && info.worker_id == 0 && !ctx.get_string("report_prefix").empty()) {
-        io::ofstream out(ctx.get_string("report_prefix") + "_" + ctx.get_string("my_id"), std::ios_base::out | std::ios_base::app);
+      if (report_interval > 0 && (i + 1) % report_interval == 0 && info.worker_id == 0
+          && !ctx.get_string("report_prefix").empty()) {
+        io::ofstream out(ctx.get_string("report_prefix") + "_" + ctx.get_string("my_id"),
+            std::ios_base::out | std::ios_base::app);
         out << i + 1 << "\t" << elapsed_ms() << "\n";
       }
       if (p_straggle > 0 && std::uniform_real_distribution<double>(0, 1)(rng) < p_straggle)
@@ -241,7 +246,8 @@ int main(int argc, char** argv) {
   MINIPS_CHECK(CheckValidNodeIds(nodes) && CheckUniquePort(nodes));
   Node scale_node;
   if (ctx.get_bool("scale") && !ctx.get_string("scale_name").empty()) {
-    scale_node = Node{static_cast<uint32_t>(ctx.get_int32("my_id")), ctx.get_string("scale_name"), ctx.get_int32("scale_port")};
+    scale_node = Node{static_cast<uint32_t>(ctx.get_int32("my_id")), ctx.get_string("scale_name"),
+        ctx.get_int32("scale_port")};
     if (!ctx.get_string("scale_file").empty()) lib::SVMDumper::DumpScaleFile(scale_node, ctx.get_string("scale_file"));
     ctx.set("has_scale_node", true);
     ctx.set("scale_node_id", static_cast<int32_t>(scale_node.id));

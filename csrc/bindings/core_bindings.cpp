@@ -63,7 +63,8 @@ PYBIND11_MODULE(_minips_core, m) {
       .def("end", &Range::end)
       .def("size", &Range::size);
 
-  py::enum_<ModelType>(m, "ModelType").value("SSP", ModelType::SSP).value("BSP", ModelType::BSP).value("ASP", ModelType::ASP);
+  py::enum_<ModelType>(m, "ModelType").value("SSP", ModelType::SSP).value("BSP", ModelType::BSP).value("ASP",
+      ModelType::ASP);
   py::enum_<StorageType>(m, "StorageType").value("Map", StorageType::Map).value("Vector", StorageType::Vector);
 
   // ---- node utils / flags / context
@@ -81,7 +82,8 @@ PYBIND11_MODULE(_minips_core, m) {
   m.def("check_fault_tolerance", &CheckFaultTolerance);
   m.def("resolve_path", &io::ResolvePath);
 
-  m.def("define_flag", [](const std::string& n, const std::string& d, const std::string& h) { Flags::Get().Define(n, d, h); },
+  m.def("define_flag", [](const std::string& n, const std::string& d, const std::string& h) { Flags::Get().Define(n,
+      d, h); },
         py::arg("name"), py::arg("default"), py::arg("help") = "");
   m.def("parse_flags", [](const std::vector<std::string>& args) { return Flags::Get().Parse(args); });
   m.def("all_flags", [] { return Flags::Get().All(); });
@@ -150,8 +152,10 @@ PYBIND11_MODULE(_minips_core, m) {
     if (!lib::Parser::parse_libsvm(line, &item)) return py::none();
     return py::cast(std::make_pair(item.first, item.second));
   });
-  m.def("load_config_data", [](const std::string& p) { return lib::SVMDumper::LoadConfigData(p); }, py::arg("path") = "");
-  m.def("dump_config_data", [](const std::map<int, int>& m2, const std::string& p) { lib::SVMDumper::DumpConfigData(m2, p); },
+  m.def("load_config_data", [](const std::string& p) { return lib::SVMDumper::LoadConfigData(p); },
+      py::arg("path") = "");
+  m.def("dump_config_data", [](const std::map<int, int>& m2,
+      const std::string& p) { lib::SVMDumper::DumpConfigData(m2, p); },
         py::arg("iter_map"), py::arg("path") = "");
 
   // ---- engine
@@ -172,7 +176,8 @@ PYBIND11_MODULE(_minips_core, m) {
   py::class_<Info>(m, "Info")
       .def_readonly("thread_id", &Info::thread_id)
       .def_readonly("worker_id", &Info::worker_id)
-      .def("create_kv_client_table", [](const Info& info, uint32_t table_id) { return info.CreateKVClientTable<double>(table_id); })
+      .def("create_kv_client_table", [](const Info& info,
+          uint32_t table_id) { return info.CreateKVClientTable<double>(table_id); })
       .def("debug_string", &Info::DebugString);
 
   py::class_<MLTask>(m, "MLTask")
@@ -190,13 +195,15 @@ PYBIND11_MODULE(_minips_core, m) {
       .def("is_setup", &MLTask::IsSetup);
 
   py::class_<Engine>(m, "Engine")
-      .def(py::init([](const Node& node, const std::vector<Node>& nodes, const Node& master) { return new Engine(node, nodes, master); }),
+      .def(py::init([](const Node& node, const std::vector<Node>& nodes,
+          const Node& master) { return new Engine(node, nodes, master); }),
            py::arg("node"), py::arg("nodes"), py::arg("master_node") = Node())
       .def("start_everything", &Engine::StartEverything, py::arg("num_server_threads_per_node") = 1,
            py::call_guard<py::gil_scoped_release>())
       .def("stop_everything", &Engine::StopEverything, py::call_guard<py::gil_scoped_release>())
       .def("create_table",
-           [](Engine& e, const std::vector<std::pair<uint64_t, uint64_t>>& ranges, ModelType mt, StorageType st, int staleness) {
+           [](Engine& e, const std::vector<std::pair<uint64_t, uint64_t>>& ranges, ModelType mt, StorageType st,
+               int staleness) {
              std::vector<Range> r;
              for (auto& p : ranges) r.emplace_back(p.first, p.second);
              return e.CreateTable<double>(r, mt, st, staleness);

@@ -62,7 +62,8 @@ std::vector<uint32_t> SimpleIdMapper::GetWorkerHelperThreadsForId(uint32_t node_
 }
 std::vector<uint32_t> SimpleIdMapper::GetWorkerThreadsForId(uint32_t node_id) const {
   auto it = node2worker_.find(node_id);
-  return it == node2worker_.end() ? std::vector<uint32_t>() : std::vector<uint32_t>(it->second.begin(), it->second.end());
+  return it == node2worker_.end() ? std::vector<uint32_t>() : std::vector<uint32_t>(it->second.begin(),
+      it->second.end());
 }
 std::vector<uint32_t> SimpleIdMapper::GetAllServerThreads() const {
   std::vector<uint32_t> out;
@@ -133,7 +134,8 @@ void Engine::StartEverything(int num_server_threads_per_node) {
 
 void Engine::StopEverything() {
   StopHeartbeatThread();  // queues the goodbye heartbeat on the sender
-  StopSender();           // drains the sender queue (the goodbye must leave before the sockets close; engine.hpp:174-180)
+  // drains the sender queue (the goodbye must leave before the sockets close; engine.hpp:174-180)
+  StopSender();
   StopMailbox();          // barrier, stop receiver, kExit into every registered queue (servers, helper)
   StopServerThreads();
   StopWorkerThreads();

@@ -50,7 +50,8 @@ bool ReadAll(int fd, void* buf, size_t n) {
 bool SendFrame(int fd, int type, const BinStream& body) {
   const int32_t t = type;
   const uint64_t n = body.size();
-  return WriteAll(fd, &t, sizeof(t)) && WriteAll(fd, &n, sizeof(n)) && (n == 0 || WriteAll(fd, body.get_remained_buffer(), n));
+  return WriteAll(fd, &t, sizeof(t)) && WriteAll(fd, &n, sizeof(n)) && (n == 0 || WriteAll(fd,
+      body.get_remained_buffer(), n));
 }
 bool RecvFrame(int fd, int* type, BinStream* body) {
   int32_t t = 0;
@@ -67,7 +68,10 @@ bool RecvFrame(int fd, int* type, BinStream* body) {
 
 // ------------------------------------------------------------------ Coordinator
 Coordinator::Coordinator(int proc_id, std::string hostname, std::string master_host, int master_port)
-    : proc_id_(proc_id), hostname_(std::move(hostname)), master_host_(std::move(master_host)), master_port_(master_port) {}
+    : proc_id_(proc_id),
+      hostname_(std::move(hostname)),
+      master_host_(std::move(master_host)),
+      master_port_(master_port) {}
 
 Coordinator::~Coordinator() {
   if (fd_ >= 0) ::close(fd_);
@@ -88,7 +92,8 @@ void Coordinator::serve() {
     if (::connect(fd_, res->ai_addr, res->ai_addrlen) == 0) break;
     ::close(fd_);
     fd_ = -1;
-    MINIPS_CHECK(std::chrono::steady_clock::now() < deadline) << "block assigner at " << master_host_ << ":" << master_port_ << " unreachable";
+    MINIPS_CHECK(std::chrono::steady_clock::now() < deadline)
+        << "block assigner at " << master_host_ << ":" << master_port_ << " unreachable";
     std::this_thread::sleep_for(std::chrono::milliseconds(20));
   }
   ::freeaddrinfo(res);

@@ -303,7 +303,8 @@ void Mailbox::Dispatch(Message& msg) {
       if (listener_) listener_->OnRollBack(msg.meta.failed_node_id >= 0 ? msg.meta.failed_node_id : msg.meta.sender);
       return;
     case Flag::kScaleRollback:
-      if (listener_) listener_->OnScaleRollBack(msg.meta.failed_node_id >= 0 ? msg.meta.failed_node_id : msg.meta.sender);
+      if (listener_) listener_->OnScaleRollBack(msg.meta.failed_node_id >= 0 ? msg.meta.failed_node_id
+          : msg.meta.sender);
       return;
     case Flag::kCheckpoint: {
       // requests travel worker -> server thread; acks travel back to a user thread id
@@ -384,7 +385,8 @@ void Mailbox::Barrier() {
   }
   std::unique_lock<std::mutex> lk(barrier_mu_);
   // nodes_ may shrink while we wait (ForceQuit); re-evaluate the target on every wake-up
-  barrier_cv_.wait(lk, [this] { return barrier_count_ >= static_cast<int>(nodes_.size()) + (has_scale_node_ ? 1 : 0); });
+  barrier_cv_.wait(lk, [this] { return barrier_count_ >= static_cast<int>(nodes_.size()) + (has_scale_node_ ? 1
+      : 0); });
   barrier_count_ -= static_cast<int>(nodes_.size()) + (has_scale_node_ ? 1 : 0);
   if (barrier_count_ < 0) barrier_count_ = 0;
 }

@@ -22,7 +22,8 @@ __device__ __forceinline__ uint32_t hash32(uint32_t x) {
 }
 __device__ __forceinline__ uint32_t cas_sys(uint32_t* p, uint32_t expected, uint32_t desired) {
   uint32_t old;
-  asm volatile("atom.relaxed.sys.global.cas.b32 %0, [%1], %2, %3;" : "=r"(old) : "l"(p), "r"(expected), "r"(desired) : "memory");
+  asm volatile("atom.relaxed.sys.global.cas.b32 %0, [%1], %2, %3;" : "=r"(old) : "l"(p), "r"(expected), "r"(desired)
+      : "memory");
   return old;
 }
 __device__ __forceinline__ uint32_t ld_key_sys(const uint32_t* p) {
@@ -57,7 +58,8 @@ __device__ __forceinline__ int64_t find_only(const uint32_t* keys, uint32_t cap_
 }
 
 __global__ void __launch_bounds__(256)
-hash_add_kernel(const __grid_constant__ MpsHashView v, const uint32_t* __restrict__ keys, const float* __restrict__ vals,
+hash_add_kernel(const __grid_constant__ MpsHashView v, const uint32_t* __restrict__ keys,
+    const float* __restrict__ vals,
                 int64_t n, int* __restrict__ overflow) {
   const int64_t stride = static_cast<int64_t>(gridDim.x) * blockDim.x;
   for (int64_t i = static_cast<int64_t>(blockIdx.x) * blockDim.x + threadIdx.x; i < n; i += stride) {
@@ -101,7 +103,8 @@ __global__ void hash_clear_kernel(uint32_t* keys, float* vals, int64_t cap) {
 
 // compacts the live (key, value) pairs of one LOCAL shard (checkpoint dump / size)
 __global__ void hash_export_kernel(const uint32_t* __restrict__ keys, const float* __restrict__ vals, int64_t cap,
-                                   uint32_t* __restrict__ out_keys, float* __restrict__ out_vals, int* __restrict__ count) {
+                                   uint32_t* __restrict__ out_keys, float* __restrict__ out_vals,
+                                   int* __restrict__ count) {
   const int64_t stride = static_cast<int64_t>(gridDim.x) * blockDim.x;
   for (int64_t i = static_cast<int64_t>(blockIdx.x) * blockDim.x + threadIdx.x; i < cap; i += stride) {
     const uint32_t k = keys[i];

@@ -340,7 +340,8 @@ kmeans_assign_ref_kernel(const __nv_bfloat16* __restrict__ x, const __nv_bfloat1
   int bi = 0;
   for (int k = 0; k < K; ++k) {
     float acc = 0.f;
-    for (int d = 0; d < D; ++d) acc = fmaf(__bfloat162float(x[row * D + d]), __bfloat162float(c[static_cast<int64_t>(k) * D + d]), acc);
+    for (int d = 0; d < D; ++d) acc = fmaf(__bfloat162float(x[row * D + d]),
+        __bfloat162float(c[static_cast<int64_t>(k) * D + d]), acc);
     const float v = acc + cnorm[k];  // c is stored as bf16(-2 c)
     if (v < best) { best = v; bi = k; }
   }

@@ -29,7 +29,11 @@ template <> struct Chunk<double> {
 
 // strong system-scope chunk load (peer shard or peer scratch)
 __device__ __forceinline__ Chunk<float> ld_sys_chunk(const float* p) { Chunk<float> c; c.v = ld_sys_v4(p); return c; }
-__device__ __forceinline__ Chunk<double> ld_sys_chunk(const double* p) { Chunk<double> c; c.v = ld_sys_v2(p); return c; }
+__device__ __forceinline__ Chunk<double> ld_sys_chunk(const double* p) {
+  Chunk<double> c;
+  c.v = ld_sys_v2(p);
+  return c;
+}
 // L2 (cache-global) chunk load of local memory other CTAs have been adding into
 __device__ __forceinline__ Chunk<float> ld_cg_chunk(const float* p) { Chunk<float> c; c.v = ld_cg_v4(p); return c; }
 __device__ __forceinline__ Chunk<double> ld_cg_chunk(const double* p) {

@@ -352,7 +352,8 @@ int mps_batch_unique_keys(const MpsCsr* csr, int64_t row_begin, int64_t batch, u
   const int grid = static_cast<int>(want < 1 ? 1 : (want < sms * 8 ? want : sms * 8));
   mps::mark_keys_kernel<<<grid, 256, 0, st>>>(*csr, row_begin, batch, num_dims, bitmap);
   MPS_LAUNCH_CHECK();
-  int rc = mps::exclusive_scan(mps::PopcWord{bitmap}, mps::EmitKeys{bitmap, word_prefix, keys_out}, words, tile_sums, st);
+  int rc = mps::exclusive_scan(mps::PopcWord{bitmap}, mps::EmitKeys{bitmap, word_prefix, keys_out}, words, tile_sums,
+      st);
   if (rc) return rc;
   MPS_CHECK(cudaMemcpyAsync(count_out, tile_sums + n_tiles, sizeof(uint32_t), cudaMemcpyDeviceToDevice, st));
   if (slots_out) {

@@ -102,7 +102,9 @@ static void ResetWorkers(AbstractModel* model, ThreadsafeQueue<Message>* q, std:
   q->WaitAndPop(&ack);
   EXPECT_TRUE(ack.meta.flag == Flag::kResetWorkerInModel);
 }
-static int PortBase() { return 20000 + (static_cast<int>(::getpid()) % 1000) * 20; }
+// below the kernel's ephemeral range (32768+): an outgoing connection of an earlier case must never own a
+// port that a later case binds
+static int PortBase() { return 20000 + (static_cast<int>(::getpid()) % 600) * 20; }
 static std::string TmpDir() {
   std::string d = "/tmp/minips_core_tests_" + std::to_string(::getpid()) + "/";
   io::MakeDirsFor(d + "x");
@@ -120,7 +122,8 @@ TEST(Message, BasicNotBreakDown) {
 }
 
 // base/range_partition_manager_test.cpp:21-64
-TEST(RangePartitionManager, Init) { RangePartitionManager pm({0, 1, 2}, {{2, 4}, {4, 7}, {7, 10}}); EXPECT_EQ(pm.GetNumServers(), 3u); }
+TEST(RangePartitionManager, Init) { RangePartitionManager pm({0, 1, 2}, {{2, 4}, {4, 7}, {7,
+    10}}); EXPECT_EQ(pm.GetNumServers(), 3u); }
 TEST(RangePartitionManager, SliceKeys) {
   RangePartitionManager pm({0, 1, 2}, {{2, 4}, {4, 7}, {7, 10}});
   SArray<Key> keys({2, 8, 9});
@@ -607,7 +610,8 @@ static void MultiNodeBarrier(int n_nodes, int port0, int rounds, bool also_send)
         mb.Send(m);
         Message r;
         q.WaitAndPop(&r);
-        if (r.meta.sender == (i + n_nodes - 1) % n_nodes && SArray<Key>(r.data[0])[0] == static_cast<Key>(r.meta.sender)) ++ok;
+        if (r.meta.sender == (i + n_nodes - 1) % n_nodes
+            && SArray<Key>(r.data[0])[0] == static_cast<Key>(r.meta.sender)) ++ok;
       } else {
         ++ok;
       }
@@ -890,7 +894,8 @@ TEST(BinStream, RoundTrips) {
   BinStream s;
   std::map<std::string, std::vector<int>> m{{"a", {1, 2}}, {"b", {}}};
   std::vector<bool> bits{true, false, true};
-  s << 42 << 2.5 << std::string("hello") << m << bits << std::make_pair(7, std::string("x")) << SArray<float>({1.f, 2.f});
+  s << 42 << 2.5 << std::string("hello") << m << bits << std::make_pair(7, std::string("x")) << SArray<float>({1.f,
+      2.f});
   BinStream inner;
   inner << 1 << 2;
   s << inner;
@@ -933,7 +938,8 @@ TEST(Context, FlagsAndIterationMap) {
   Flags::Get().Define("num_dims", "123");
   Flags::Get().Define("scale", "false");
   Flags::Get().Define("alpha", "0.1");
-  auto pos = Flags::Get().Parse(std::vector<std::string>{"--num_dims=456", "--config_file", "cfg", "--scale", "pos", "--my_id=2"});
+  auto pos = Flags::Get().Parse(std::vector<std::string>{"--num_dims=456", "--config_file", "cfg", "--scale", "pos",
+      "--my_id=2"});
   auto& ctx = Context::get_instance();
   EXPECT_EQ(ctx.get_int32("num_dims"), 456);
   EXPECT_EQ(ctx.get_string("config_file"), std::string("cfg"));
@@ -1335,7 +1341,8 @@ TEST(Lib, AsyncDataLoaderPrefetchesBatches) {
   Coordinator coord(0, "localhost", "localhost", PortBase() + 18);
   coord.serve();
   LineInputFormat in(&coord, f, 1, 256);
-  lib::AsyncDataLoader<SVMItem> loader(&in, [](const std::string& l, SVMItem* s) { return lib::Parser::parse_libsvm(l, s); }, 10, 3);
+  lib::AsyncDataLoader<SVMItem> loader(&in, [](const std::string& l,
+      SVMItem* s) { return lib::Parser::parse_libsvm(l, s); }, 10, 3);
   size_t total = 0, batches = 0;
   std::vector<SVMItem> batch;
   while (loader.get_data(&batch)) {

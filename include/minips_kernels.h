@@ -31,7 +31,8 @@ extern "C" {
 #define MPS_PAD_ERROR (MPS_PAD_BARRIER + MPS_MAX_RANKS)      /* [1] sticky error (timeout) flag   */
 #define MPS_PAD_MINCLOCK (MPS_PAD_ERROR + 1)                 /* [1] last min clock seen (debug)   */
 #define MPS_PAD_LOCALCTR (MPS_PAD_MINCLOCK + 1)              /* [4] local CTA-completion counters */
-#define MPS_PAD_XCNT (MPS_PAD_LOCALCTR + 4)                   /* [2 sets][ready|arrived][MPS_MAX_RANKS] LR exchange: CTAs of rank r done */
+/* LR exchange kernel: [2 sets][ready | arrived][MPS_MAX_RANKS] = CTAs of rank r that are done */
+#define MPS_PAD_XCNT (MPS_PAD_LOCALCTR + 4)
 #define MPS_PAD_INTS 1024                                    /* pad size in int32 (4 KiB)         */
 
 enum { MPS_MODEL_SSP = 0, MPS_MODEL_BSP = 1, MPS_MODEL_ASP = 2 }; /* driver/engine.hpp:25-27 */
@@ -343,7 +344,8 @@ int mps_kmeans_delta_push(const MpsTableView* centers_view, const MpsTableView* 
                           const MpsClockView* counts_clk, int progress, const float* centers,
                           float* sums, float* counts_batch, int K, int D, float alpha, void* stream);
 /* One whole mini-batch iteration of a worker (kmeans.cpp:216-275) enqueued by a single host call:
- * assign (centre pull fused) -> accumulate (sorted, see above) -> delta + push of both tables -> Clock of both tables at
+ * assign (centre pull fused) -> accumulate (sorted,
+     see above) -> delta + push of both tables -> Clock of both tables at
  * progress + 1 (fold: this worker is the last local one to clock, see mps_clock). */
 int mps_kmeans_step(const MpsTableView* centers_view, const MpsClockView* centers_clk,
                     const MpsTableView* counts_view, const MpsClockView* counts_clk, int worker,

@@ -32,7 +32,8 @@ class DenseLRTrainer:
         self.grad = torch.zeros(self.D, dtype=torch.float32, device=self.dev)
         self._coef: Optional[torch.Tensor] = None
 
-    def forward(self, start: int, batch: int, loss: Optional[torch.Tensor] = None, weights: Optional[torch.Tensor] = None):
+    def forward(self, start: int, batch: int, loss: Optional[torch.Tensor] = None,
+        weights: Optional[torch.Tensor] = None):
         """coef = alpha (y - sigmoid(X w)) for rows [start, start+batch); returns (coef, loss[2])."""
         xb = self.x[start:start + batch]
         n = xb.shape[0]
@@ -49,9 +50,11 @@ class DenseLRTrainer:
         else:
             wptr = C.c_void_p(weights.data_ptr())
         _lib.check(self.lib.mps_dense_lr_forward_tc(
-            view, clk, c.progress, wptr, C.c_void_p(xb.data_ptr()), C.c_void_p(self.label[start:start + batch].data_ptr()),
+            view, clk, c.progress, wptr, C.c_void_p(xb.data_ptr()),
+            C.c_void_p(self.label[start:start + batch].data_ptr()),
             n, self.D, self.alpha, C.c_void_p(self.w16.data_ptr()), C.c_void_p(self.w32.data_ptr()),
-            C.c_void_p(self.sync.data_ptr()), C.c_void_p(self._coef.data_ptr()), C.c_void_p(loss.data_ptr()), 0, c._sp()),
+            C.c_void_p(self.sync.data_ptr()), C.c_void_p(self._coef.data_ptr()), C.c_void_p(loss.data_ptr()), 0,
+            c._sp()),
             "dense_lr_forward_tc")
         return self._coef, loss
 
@@ -60,7 +63,8 @@ class DenseLRTrainer:
         coef, loss = self.forward(start, batch, loss)
         xb = self.x[start:start + batch]
         _lib.check(self.lib.mps_dense_lr_grad(C.c_void_p(xb.data_ptr()), C.c_void_p(coef.data_ptr()), xb.shape[0],
-                                              self.D, C.c_void_p(self.grad.data_ptr()), self.client._sp()), "dense_lr_grad")
+                                              self.D, C.c_void_p(self.grad.data_ptr()), self.client._sp()),
+                   "dense_lr_grad")
         self.client.add_all(self.grad, zero_src=True)
         self.client.clock()
         return loss

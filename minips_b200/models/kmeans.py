@@ -54,7 +54,8 @@ class KMeansAssigner:
         assert x.dtype == torch.bfloat16 and x.is_contiguous() and x.shape[1] == self.D
         n = x.shape[0]
         if out is None:
-            out = (torch.empty(n, dtype=torch.int32, device=self.dev), torch.empty(n, dtype=torch.float32, device=self.dev))
+            out = (torch.empty(n, dtype=torch.int32, device=self.dev), torch.empty(n, dtype=torch.float32,
+                device=self.dev))
         assign, dist = out
         view = clk = None
         progress = 0
@@ -150,7 +151,8 @@ class KMeansTrainer:
 
     def _fusable(self) -> bool:
         tc, tn = self.tc.table, self.tn.table
-        return (self.allow_fused and len(tc.local_workers) <= 1 and len(tn.local_workers) <= 1 and tc.dtype == torch.float32
+        return (self.allow_fused and len(tc.local_workers) <= 1 and len(tn.local_workers) <= 1
+                and tc.dtype == torch.float32
                 and tn.dtype == torch.float32 and tc.hview is None and tn.hview is None
                 and tc.model_type == tn.model_type and self.tc.progress == self.tn.progress
                 and self.tc.stream is self.tn.stream)

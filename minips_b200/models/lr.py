@@ -269,7 +269,8 @@ class SparseLRTrainer:
         csr = self.data.c_struct()
         t = self.table
         assert weights.dtype == t.dtype and weights.numel() == t.num_keys
-        _lib.check(self.lib.mps_lr_eval(C.c_void_p(weights.data_ptr()), _lib.F32 if t.dtype == torch.float32 else _lib.F64,
+        _lib.check(self.lib.mps_lr_eval(C.c_void_p(weights.data_ptr()),
+            _lib.F32 if t.dtype == torch.float32 else _lib.F64,
                                         t.ranges[0][0], t.num_keys, C.byref(csr), 0, n,
                                         C.c_void_p(out.data_ptr()), self.client._sp()), "lr_eval")
         o = out.tolist()

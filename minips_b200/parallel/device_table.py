@@ -86,7 +86,8 @@ class DeviceTable:
             assert dtype == torch.float32 and self.k == 1
         for s, (b, e) in enumerate(self.ranges):
             r = self.shard_owner[s]
-            nbytes = _align((e - b) * self.k * self.itemsize) if not self.hash_capacity else _align(self.hash_capacity * 8)
+            nbytes = (_align((e - b) * self.k * self.itemsize) if not self.hash_capacity
+                      else _align(self.hash_capacity * 8))
             self.woff[s] = per_rank[r]
             per_rank[r] += nbytes
             if bsp:
@@ -184,7 +185,8 @@ class DeviceTable:
         count = torch.zeros(1, dtype=torch.int32, device=dev)
         base = self.slab.local_ptr + self.woff[s]
         _lib.check(self.lib.mps_hash_export(C.c_void_p(base), C.c_void_p(base + self.hash_capacity * 4),
-                                            self.hash_capacity, C.c_void_p(keys.data_ptr()), C.c_void_p(vals.data_ptr()),
+                                            self.hash_capacity, C.c_void_p(keys.data_ptr()),
+                                            C.c_void_p(vals.data_ptr()),
                                             C.c_void_p(count.data_ptr()), _lib.stream_ptr()), "hash_export")
         n = int(count.item())
         k64 = keys[:n].to(torch.int64) & 0xFFFFFFFF

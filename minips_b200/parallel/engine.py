@@ -56,7 +56,8 @@ class Engine:
         self.node = node
         self.nodes = sorted(nodes, key=lambda n: n.id)
         self.master_node = master_node
-        self.device = device if device is not None else (torch.cuda.current_device() if torch.cuda.is_available() else 0)
+        self.device = device if device is not None else (
+            torch.cuda.current_device() if torch.cuda.is_available() else 0)
         self._group = group
         self.control: Optional[_ControlPlane] = None
         self.id_mapper: Optional[SimpleIdMapper] = None

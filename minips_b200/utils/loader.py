@@ -71,7 +71,8 @@ class AsyncBatchLoader:
     def __init__(self, host, batch: int, device, depth: int = 2, in_place: bool = False):
         self.packed = isinstance(host, PackedCsrHost)
         if self.packed:
-            assert host.row_len.is_pinned() and host.ids.is_pinned() and host.val.is_pinned() and host.label_u8.is_pinned()
+            assert host.row_len.is_pinned() and host.ids.is_pinned() and host.val.is_pinned()
+            assert host.label_u8.is_pinned()
         else:
             assert host.row_ptr.is_pinned() and host.col.is_pinned() and host.val.is_pinned() and host.label.is_pinned()
         self.host = host

@@ -11,7 +11,8 @@ ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 REF_BIN = os.path.join(ROOT, "baseline", "_ref", "bin", "LRExample")
 
 
-@pytest.mark.skipif(not os.path.exists(REF_BIN), reason="reference shim build not present (baseline/ref_build/build_ref.py)")
+@pytest.mark.skipif(not os.path.exists(REF_BIN),
+    reason="reference shim build not present (baseline/ref_build/build_ref.py)")
 def test_reference_arm_small_run(tmp_path):
     env = dict(os.environ, MINIPS_REF_DATA_DIR=str(tmp_path), MINIPS_REF_WORKERS_PER_NODE="1",
                MINIPS_REF_TIMEOUT="150")

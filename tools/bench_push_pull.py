@@ -69,8 +69,10 @@ def main():
         for op, ms in (("pull", ms_pull), ("push", ms_push)):
             payload = num_dims * 4
             roof_ms = payload * remote / (NVLINK_GBS * 1e6) if world > 1 else None
-            rows.append({"op": op, "pattern": "contiguous", "keys": num_dims, "ms": ms, "Mkeys_per_s": num_dims / ms / 1e3,
-                         "payload_GBps": payload / ms / 1e6, "nvlink_roofline_frac": (roof_ms / ms) if roof_ms else None})
+            rows.append({"op": op, "pattern": "contiguous", "keys": num_dims, "ms": ms,
+                "Mkeys_per_s": num_dims / ms / 1e3,
+                         "payload_GBps": payload / ms / 1e6,
+                         "nvlink_roofline_frac": (roof_ms / ms) if roof_ms else None})
 
     task = MLTask()
     task.set_worker_alloc([WorkerAlloc(n.id, 1) for n in engine.nodes])
@@ -82,7 +84,8 @@ def main():
         print(json.dumps({"bench": "push_pull_micro", "n_gpus": world, "table_keys": num_dims, "rows": rows}))
         for r in rows:
             frac = f"{r['nvlink_roofline_frac']:.2f}" if r["nvlink_roofline_frac"] is not None else "  - "
-            print(f"{r['op']:5s} {r['pattern']:10s} keys={r['keys']:>10d}  {r['ms']:9.4f} ms  {r['Mkeys_per_s']:10.1f} Mkeys/s"
+            print(f"{r['op']:5s} {r['pattern']:10s} keys={r['keys']:>10d}  {r['ms']:9.4f} ms  "
+                  f"{r['Mkeys_per_s']:10.1f} Mkeys/s"
                   f"  {r['payload_GBps']:8.1f} GB/s  roofline {frac}", file=sys.stderr)
     import torch.distributed as dist
     if dist.is_initialized():

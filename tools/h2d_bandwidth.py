@@ -38,7 +38,8 @@ def bw(host_parts, dev_parts, iters=50):
 torch.cuda.init()
 torch.zeros(1, device="cuda")
 sizes = [65536, 6_553_600, 10_485_760, 65536]  # row_len, packed ids, values, labels of one step
-for name, alloc in (("pin_memory", lambda n: torch.empty(n, dtype=torch.uint8).pin_memory()), ("write-combined", wc_pinned)):
+for name, alloc in (("pin_memory", lambda n: torch.empty(n, dtype=torch.uint8).pin_memory()), ("write-combined",
+    wc_pinned)):
     host = [alloc(n) for n in sizes]
     for h in host:
         h.fill_(1)

@@ -81,8 +81,11 @@ engine.run(task)
 engine.stop_everything()
 gb = B * a.D * 2 / 1e9
 print(f"dense LR, batch {B} x D {a.D} bf16 ({gb:.2f} GB per pass), HBM copy peak {HBM_GBS:.0f} GB/s")
-print(f"  forward (tcgen05, pull + sigmoid/loss fused): {out['forward_ms']:.3f} ms  {gb / out['forward_ms'] * 1e3:.0f} GB/s"
-      f"  = {gb / out['forward_ms'] * 1e3 / HBM_GBS:.2f} of HBM copy peak   [torch matmul+sigmoid: {out['torch_forward_ms']:.3f} ms]")
-print(f"  iteration (Get, forward, gradient, Add, Clock): {out['step_ms']:.3f} ms  {2 * gb / out['step_ms'] * 1e3:.0f} GB/s"
+print(f"  forward (tcgen05, pull + sigmoid/loss fused): {out['forward_ms']:.3f} ms  "
+      f"{gb / out['forward_ms'] * 1e3:.0f} GB/s"
+      f"  = {gb / out['forward_ms'] * 1e3 / HBM_GBS:.2f} of HBM copy peak   "
+      f"[torch matmul+sigmoid: {out['torch_forward_ms']:.3f} ms]")
+print(f"  iteration (Get, forward, gradient, Add, Clock): {out['step_ms']:.3f} ms  "
+      f"{2 * gb / out['step_ms'] * 1e3:.0f} GB/s"
       f"  = {2 * gb / out['step_ms'] * 1e3 / HBM_GBS:.2f} of HBM copy peak   {B / out['step_ms'] / 1e6:.2f} G samples/s"
       f"   [torch: {out['torch_step_ms']:.3f} ms, {B / out['torch_step_ms'] / 1e6:.2f} G samples/s]")

@@ -47,7 +47,8 @@ if a.ncu:
     sys.exit(0)
 
 ms = timed(lambda: km.assign(x, centers=centers, out=out))
-print(f"tcgen05 assign   n={a.n} K={a.K} D={a.D}: {ms:8.3f} ms  {flops / ms / 1e9:8.1f} TFLOP/s  {a.n / ms / 1e3:8.1f} Mpoints/s")
+print(f"tcgen05 assign   n={a.n} K={a.K} D={a.D}: {ms:8.3f} ms  {flops / ms / 1e9:8.1f} TFLOP/s  "
+      f"{a.n / ms / 1e3:8.1f} Mpoints/s")
 
 nr = min(a.n, 200_000)
 ms_r = timed(lambda: km.assign_ref(x[:nr]), iters=2, warm=1)

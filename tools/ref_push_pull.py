@@ -67,7 +67,8 @@ def main():
     if not os.path.exists(EXE):
         raise SystemExit("build first: python baseline/ref_build/build_ref.py")
     lines = [f"# reference (MiniPs, ZMQ over localhost, CPU) push/pull; host cores: {os.cpu_count()}",
-             "# per node: keys/s = n / median time, slowest node; GB/s counts 12 bytes per key (uint32 key + double value)",
+             "# per node: keys/s = n / median time, slowest node; GB/s counts 12 bytes per key "
+             "(uint32 key + double value)",
              f"{'nodes':>5} {'mode':>7} {'keys':>9} {'push_ms':>10} {'push_Mkeys/s':>13} {'push_GB/s':>10} "
              f"{'pull_ms':>10} {'pull_Mkeys/s':>13} {'pull_GB/s':>10} {'agg_pull_Mkeys/s':>17}"]
     for n in args.nodes:
@@ -76,7 +77,8 @@ def main():
             if cnt != n:
                 continue
             lines.append(f"{n:>5} {mode:>7} {k:>9} {push:>10.3f} {k / push / 1e3:>13.2f} {k * 12 / push / 1e6:>10.3f} "
-                         f"{pull:>10.3f} {k / pull / 1e3:>13.2f} {k * 12 / pull / 1e6:>10.3f} {n * k / pull / 1e3:>17.2f}")
+                         f"{pull:>10.3f} {k / pull / 1e3:>13.2f} {k * 12 / pull / 1e6:>10.3f} "
+                         f"{n * k / pull / 1e3:>17.2f}")
     text = "\n".join(lines)
     print(text)
     if args.out:

@@ -34,13 +34,15 @@ def host(tool: str, filt: str) -> int:
     # the distribution compiler ships libtsan / libasan; a toolchain named by $CXX may not
     cxx = os.environ.get("MINIPS_SAN_CXX") or ("/usr/bin/g++" if os.path.exists("/usr/bin/g++") else
                                                 os.environ.get("CXX", "g++"))
-    san = {"thread": ["-fsanitize=thread"], "address": ["-fsanitize=address,undefined", "-fno-omit-frame-pointer"]}[tool]
+    san = {"thread": ["-fsanitize=thread"], "address": ["-fsanitize=address,undefined",
+        "-fno-omit-frame-pointer"]}[tool]
     out_dir = os.path.join(ROOT, "build", f"san_{tool}")
     os.makedirs(out_dir, exist_ok=True)
     srcs = sorted(glob.glob(os.path.join(ROOT, "csrc", "core", "**", "*.cpp"), recursive=True))
     srcs.append(os.path.join(ROOT, "csrc", "tests", "core_tests.cpp"))
     exe = os.path.join(out_dir, "core_tests")
-    cmd = [cxx, "-std=c++17", "-O1", "-g", *san, f"-I{os.path.join(ROOT, 'csrc')}", f"-I{os.path.join(ROOT, 'csrc', 'core')}",
+    cmd = [cxx, "-std=c++17", "-O1", "-g", *san, f"-I{os.path.join(ROOT, 'csrc')}",
+        f"-I{os.path.join(ROOT, 'csrc', 'core')}",
            f"-I{os.path.join(ROOT, 'include')}", *srcs, "-o", exe, "-pthread"]
     print("building", exe, flush=True)
     p = subprocess.run(cmd, capture_output=True, text=True)
