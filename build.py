@@ -126,7 +126,9 @@ def build_core(force=False, verbose=True):
             if verbose:
                 print(f"[g++] {name}")
     if bind_src.exists() and (force or jobs or not mod.exists()):
-        _run([CXX, "-shared", "-o", mod, bind_obj, *objs, "-pthread"])
+        # --exclude-libs: a toolchain that links libstdc++ statically would otherwise export its copy, and
+        # torch's (system) libstdc++ interposes half of it at run time — crashes in the first ostringstream
+        _run([CXX, "-shared", "-o", mod, bind_obj, *objs, "-pthread", "-Wl,--exclude-libs,ALL"])
         if verbose:
             print(f"[link] {mod.relative_to(ROOT)}")
     # executables

@@ -221,5 +221,29 @@ PYBIND11_MODULE(_minips_core, m) {
       .def("start_master", &Master::StartMaster, py::call_guard<py::gil_scoped_release>())
       .def("stop_master", &Master::StopMaster, py::call_guard<py::gil_scoped_release>())
       .def("shutdown", &Master::Shutdown, py::call_guard<py::gil_scoped_release>())
-      .def("rollback", &Master::RollBack);
+      .def("rollback", &Master::RollBack, py::call_guard<py::gil_scoped_release>())
+      .def("set_rollback_hook",
+           [](Master& m2, py::function fn) {
+             // runs on the master thread: take the GIL for the duration of the Python callback
+             auto shared = std::make_shared<py::function>(std::move(fn));
+             m2.SetRollBackHook([shared](uint32_t failed) {
+               py::gil_scoped_acquire gil;
+               (*shared)(failed);
+             });
+           })
+      .def("recovering_node", [](Master& m2) { return m2.GetMasterThread()->GetRecoveringNodeId(); })
+      .def("all_quit", [](Master& m2) { return m2.GetMasterThread()->AllQuit(); })
+      .def("heartbeats", [](Master& m2) {
+        std::map<uint32_t, long long> out;
+        for (const auto& kv : m2.GetMasterThread()->GetHeartBeats()) out[kv.first] = static_cast<long long>(kv.second);
+        return out;
+      });
+
+  py::class_<ControlAgent>(m, "ControlAgent")
+      .def(py::init<const Node&, const std::vector<Node>&, const Node&>())
+      .def("start", &ControlAgent::Start, py::call_guard<py::gil_scoped_release>())
+      .def("stop", &ControlAgent::Stop, py::arg("quit_heartbeat") = true, py::call_guard<py::gil_scoped_release>())
+      .def("need_rollback", &ControlAgent::NeedRollBack)
+      .def("clear_rollback", &ControlAgent::ClearRollBack)
+      .def("rollback_count", &ControlAgent::RollBackCount);
 }

@@ -188,13 +188,18 @@ void Engine::StartHeartbeatThread() {
       for (int i = 0; i < interval * 10 && heartbeat_running_; ++i)
         std::this_thread::sleep_for(std::chrono::milliseconds(100));
     }
-    HeartBeat(node_.id, /*quit=*/true);
+    if (heartbeat_goodbye_) HeartBeat(node_.id, /*quit=*/true);
   });
 }
 
 void Engine::StopHeartbeatThread() {
   heartbeat_running_ = false;
   if (heartbeat_thread_.joinable()) heartbeat_thread_.join();
+}
+
+void Engine::AbandonHeartbeatThread() {
+  heartbeat_goodbye_ = false;
+  StopHeartbeatThread();
 }
 
 void Engine::StopServerThreads() {
@@ -433,7 +438,12 @@ void Engine::OnForceQuit(uint32_t node_id) {
 }
 
 void Engine::OnRollBack(int failed_node_id) {
-  (void)failed_node_id;
+  // the socket to the failed node died with it; the relaunched process listens on the same address
+  // (ZMQ DEALER sockets of the reference reconnect by themselves)
+  if (mailbox_ && failed_node_id >= 0 && static_cast<uint32_t>(failed_node_id) != node_.id)
+    for (const auto& n : nodes_)
+      if (n.id == static_cast<uint32_t>(failed_node_id)) mailbox_->ConnectTo(n);
+  ++rollback_signals_;
   // every node returns to the last checkpoint (comm/mailbox.cpp:172-190)
   const auto iters = checkpoint::LoadConfigData();
   Context::get_instance().update_iteration(iters);

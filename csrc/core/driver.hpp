@@ -145,6 +145,7 @@ class Engine : public MailboxListener {
   void StartWorkerThreads();
   void StartHeartbeatThread();
   void StopHeartbeatThread();
+  void AbandonHeartbeatThread();  // stop without the goodbye message (the node is not leaving for good)
   void StopServerThreads();
   void StopWorkerThreads();
   void StopSender();
@@ -205,6 +206,7 @@ class Engine : public MailboxListener {
   WorkerThread* GetWorkerThread() { return worker_thread_.get(); }
   AbstractPartitionManager* GetPartitionManager(uint32_t table_id);
   int GetRollBackIteration() const { return rollback_iteration_; }
+  int GetRollBackSignals() const { return rollback_signals_; }  // kRollBack messages seen so far
 
  private:
   void RegisterPartitionManager(uint32_t table_id, std::unique_ptr<AbstractPartitionManager> pm);
@@ -231,6 +233,8 @@ class Engine : public MailboxListener {
   std::atomic<bool> heartbeat_running_{false};
 
   std::atomic<bool> need_rollback_{false};
+  std::atomic<int> rollback_signals_{0};
+  std::atomic<bool> heartbeat_goodbye_{true};
   std::mutex recover_mu_;
   std::condition_variable recover_cv_;
   int rollback_counter_ = 0;

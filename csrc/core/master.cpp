@@ -158,9 +158,48 @@ void Master::Shutdown() {
 
 void Master::RollBack(uint32_t failed_node_id) {
   CheckFaultTolerance(4);
+  // the socket to the failed node died with it; the relaunched process listens on the same address
+  for (const auto& n : nodes_)
+    if (n.id == failed_node_id) engine_->GetMailbox()->ConnectTo(n);
+  if (rollback_hook_) rollback_hook_(failed_node_id);
   engine_->RollBack(failed_node_id);
 }
 
 void Master::ScaleRollBack(uint32_t scale_node_id) { engine_->ScaleRollBack(scale_node_id); }
+
+// ------------------------------------------------------------------ ControlAgent
+ControlAgent::ControlAgent(const Node& node, const std::vector<Node>& nodes, const Node& master_node)
+    : node_(node), master_node_(master_node), nodes_(nodes) {
+  master_node_.is_master = true;
+}
+
+ControlAgent::~ControlAgent() {
+  try {
+    Stop(false);
+  } catch (...) {
+  }
+}
+
+void ControlAgent::Start() {
+  engine_.reset(new Engine(node_, nodes_, master_node_));
+  engine_->CreateIdMapper();
+  engine_->CreateMailbox();
+  engine_->StartSender();
+  engine_->GetMailbox()->BindAndListen();
+  engine_->GetMailbox()->StartReceiving();
+  engine_->GetMailbox()->ConnectAll();
+  engine_->StartHeartbeatThread();
+  started_ = true;
+}
+
+void ControlAgent::Stop(bool quit_heartbeat) {
+  if (!started_) return;
+  started_ = false;
+  if (quit_heartbeat) engine_->StopHeartbeatThread();  // its last message is kQuitHeartBeat
+  else engine_->AbandonHeartbeatThread();
+  engine_->StopSender();
+  engine_->GetMailbox()->StopReceiving();
+  engine_->GetMailbox()->CloseSockets();
+}
 
 }  // namespace minips

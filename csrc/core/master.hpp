@@ -70,10 +70,35 @@ class HeartBeatCheckThread {
   std::atomic<bool> running_{false};
 };
 
+// ControlAgent — the host control plane of a rank whose data plane lives elsewhere (the device backend:
+// shards in HBM, Get / Add / Clock as kernels).  It is the part of an Engine such a rank still needs:
+// the mailbox endpoint, the heartbeat to the master (driver/engine.cpp:114-148) and the rollback /
+// force-quit notifications (comm/mailbox.cpp:159-190), without server or worker threads.
+class ControlAgent {
+ public:
+  ControlAgent(const Node& node, const std::vector<Node>& nodes, const Node& master_node);
+  ~ControlAgent();
+  void Start();                       // mailbox up, connected to every node and the master, heartbeat running
+  void Stop(bool quit_heartbeat = true);
+  bool NeedRollBack() const { return engine_ && engine_->IsNeedRollBack(); }
+  void ClearRollBack() { if (engine_) engine_->SetNeedRollBack(false); }
+  int RollBackCount() const { return engine_ ? engine_->GetRollBackSignals() : 0; }
+  Engine* GetEngine() { return engine_.get(); }
+
+ private:
+  Node node_, master_node_;
+  std::vector<Node> nodes_;
+  std::unique_ptr<Engine> engine_;
+  bool started_ = false;
+};
+
 class Master {
  public:
   Master(const Node& master_node, const std::vector<Node>& nodes);
   ~Master();
+  // called on the master thread right before kRollBack is broadcast (the device backend bumps the
+  // rendezvous generation here so that every rank that receives the message finds the new one)
+  void SetRollBackHook(std::function<void(uint32_t)> f) { rollback_hook_ = std::move(f); }
   void StartMaster();                 // bring-up: id mapper + mailbox + sender + the two actors
   void StopMaster();                  // blocks until every node quit (or Shutdown was called)
   void Shutdown();                    // tear down without waiting for the nodes
@@ -88,6 +113,7 @@ class Master {
   std::unique_ptr<Engine> engine_;
   std::unique_ptr<MasterThread> master_thread_;
   std::unique_ptr<HeartBeatCheckThread> heartbeat_check_;
+  std::function<void(uint32_t)> rollback_hook_;
   bool started_ = false;
 };
 
