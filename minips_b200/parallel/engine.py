@@ -70,6 +70,7 @@ class Engine:
         self.iteration_map: Dict[int, int] = {}
         self.started = False
         self.numa = None
+        self.rank_index = 0
 
     # ---- lifecycle (engine.cpp:17-44) -------------------------------------------------------
     def start_everything(self, num_server_threads_per_node: int = 1):
@@ -81,6 +82,7 @@ class Engine:
         assert self.control.world == len(self.nodes), "one process per node expected"
         self.rank = self.control.rank
         assert self.nodes[self.rank].id == self.node.id, "node ids must be in rank order"
+        self.rank_index = self.rank
         self.num_server_threads_per_node = num_server_threads_per_node
         self.id_mapper = SimpleIdMapper(self.node, self.nodes)
         self.id_mapper.init(num_server_threads_per_node)
@@ -161,7 +163,11 @@ class Engine:
         self.worker_spec = spec
         local = spec.get_local_workers(self.node.id) if spec.has_local_workers(self.node.id) else []
         for tid in task.get_tables():
-            self.tables[tid].reset_workers(spec.num_workers, local)
+            # a restored table keeps its clocks (ssp_model.cpp:98-103: ResetWorker leaves the tracker alone
+            # under use_weight_file; progress_tracker.hpp:87-122 restores them)
+            t = self.tables[tid]
+            t.reset_workers(spec.num_workers, local, start_clock=int(getattr(t, "restored_clock", 0) or 0))
+            t.restored_clock = 0
         self.barrier()
         errors: List[BaseException] = []
         if len(local) == 1:

@@ -131,7 +131,7 @@ class FaultTolerantJob:
         engine down.  Any failure inside a generation — a device-side wait that timed out on a dead peer,
         a broken process group, an explicit RollbackSignal — is held until the master's order arrives; if
         none does within rollback_wait_s the failure is re-raised."""
-        self.resume = self.relaunched
+        self.resume = getattr(self, "resume", False) or self.relaunched
         while True:
             self._join()
             self.generations_run += 1

@@ -6,7 +6,8 @@ node with use_weight_file=True).  The master runs `relaunch_cmd + " " + <node id
 
 launch.json: {"argv": [... command line of a rank, with {id} where the node id goes ...],
               "env": {...extra environment...}, "log": "path with {id}", "device_of": {"<id>": <cuda index>}}.
-The process is started detached (the master must not wait for it) with --use_weight_file=true appended."""
+The process is started detached (the master must not wait for it) with --use_weight_file=true --relaunched=true
+appended."""
 import json
 import os
 import subprocess
@@ -16,7 +17,7 @@ import sys
 def main(argv):
     spec = json.load(open(argv[1]))
     node_id = argv[2]
-    cmd = [a.replace("{id}", node_id) for a in spec["argv"]] + ["--use_weight_file=true"]
+    cmd = [a.replace("{id}", node_id) for a in spec["argv"]] + ["--use_weight_file=true", "--relaunched=true"]
     env = dict(os.environ)
     env.update({k: str(v).replace("{id}", node_id) for k, v in spec.get("env", {}).items()})
     dev = spec.get("device_of", {}).get(node_id)

@@ -18,7 +18,7 @@ def main():
     from minips_b200 import core
     from minips_b200.parallel.fault import FaultTolerantJob
     a = json.loads(sys.argv[1])
-    relaunched = "--use_weight_file=true" in sys.argv
+    relaunched = "--relaunched=true" in sys.argv
     my_id, out = int(a["my_id"]), a["out_dir"]
     nodes = core.parse_file(a["config_file"])
     job = FaultTolerantJob(nodes, my_id, a["heartbeat_interval"], a["store_port"], relaunched=relaunched,
