@@ -265,7 +265,9 @@ __global__ void __launch_bounds__(256)
 kmeans_delta_push_kernel(const __grid_constant__ MpsTableView vc, const __grid_constant__ MpsTableView vn,
                          const __grid_constant__ MpsClockView cn, int gated, int progress,
                          const float* __restrict__ centers, float* __restrict__ sums,
-                         float* __restrict__ counts_batch, int K, int D, float alpha) {
+                         float* __restrict__ counts_batch, int K, int D, int Dv, float alpha) {
+  // K = number of real centres; `centers` / `sums` are [*, D] (padded operand layout), the table rows
+  // are Dv values long
   if (gated) cta_gate(cn, progress);
   const int lane = threadIdx.x & 31;
   const int warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
@@ -291,15 +293,16 @@ kmeans_delta_push_kernel(const __grid_constant__ MpsTableView vc, const __grid_c
       *reinterpret_cast<float4*>(sums + f) = make_float4(0.f, 0.f, 0.f, 0.f);
       // D % 4 == 0 and shard boundaries of the centre table fall on multiples of 4 values only when
       // the ranges do; route per element when the chunk straddles or is misaligned in its shard
-      const uint32_t key0 = vc.begin[0] + static_cast<uint32_t>(f);
+      const uint32_t key0 = vc.begin[0] + static_cast<uint32_t>(static_cast<int64_t>(c) * Dv + j);
       const int sc = owner_of(vc, key0);
       const int64_t off = static_cast<int64_t>(key0) - vc.begin[sc];
       float* base = static_cast<float*>(vc.staging[sc] ? vc.staging[sc] : vc.weights[sc]);
-      if (key0 + 4 <= vc.begin[sc + 1] && (off & 3) == 0) {
+      if (Dv == D && key0 + 4 <= vc.begin[sc + 1] && (off & 3) == 0) {
         if (d.x != 0.f || d.y != 0.f || d.z != 0.f || d.w != 0.f) red_sys_v4(base + off, d);
       } else {
         const float dv[4] = {d.x, d.y, d.z, d.w};
         for (int e = 0; e < 4; ++e) {
+          if (j + e >= Dv) break;  // padding columns carry no key
           const uint32_t key = key0 + e;
           const int se = owner_of(vc, key);
           float* be = static_cast<float*>(vc.staging[se] ? vc.staging[se] : vc.weights[se]);
@@ -400,32 +403,35 @@ int mps_kmeans_delta(const float* centers, const float* counts_old, const float*
 
 int mps_kmeans_delta_push(const MpsTableView* centers_view, const MpsTableView* counts_view,
                           const MpsClockView* counts_clk, int progress, const float* centers, float* sums,
-                          float* counts_batch, int K, int D, float alpha, void* stream) {
+                          float* counts_batch, int K, int D, int K_valid, int D_valid, float alpha, void* stream) {
+  const int Kv = (K_valid > 0 && K_valid <= K) ? K_valid : K;
+  const int Dv = (D_valid > 0 && D_valid <= D) ? D_valid : D;
   if (D % 4 != 0 || centers_view->dtype != MPS_F32 || counts_view->dtype != MPS_F32 ||
       centers_view->vals_per_key != 1 || counts_view->vals_per_key != 1)
     return static_cast<int>(cudaErrorInvalidValue);
-  const int grid = (K + 7) / 8;  // 8 warps per CTA, one centre row per warp
+  const int grid = (Kv + 7) / 8;  // 8 warps per CTA, one centre row per warp
   MpsClockView none{};
   mps::kmeans_delta_push_kernel<<<grid, 256, 0, static_cast<cudaStream_t>(stream)>>>(
       *centers_view, *counts_view, counts_clk ? *counts_clk : none, counts_clk != nullptr, progress, centers, sums,
-      counts_batch, K, D, alpha);
+      counts_batch, Kv, D, Dv, alpha);
   MPS_LAUNCH_CHECK();
   return 0;
 }
 
 int mps_kmeans_step(const MpsTableView* centers_view, const MpsClockView* centers_clk,
                     const MpsTableView* counts_view, const MpsClockView* counts_clk, int worker, int progress,
-                    int fold, const void* x_bf16, int64_t n, int K, int D, float alpha,
+                    int fold, const void* x_bf16, int64_t n, int K, int D, int K_valid, int D_valid, float alpha,
                     void* centers_bf16_scratch, float* cnorm_scratch, float* centers_f32, int* sync_ctr,
                     int32_t* assign, float* dist, float* sums, float* counts_batch, float* sse, int* sort_scratch,
                     void* stream) {
-  int rc = mps_kmeans_assign_tc(centers_view, centers_clk, progress, nullptr, x_bf16, n, K, D, centers_bf16_scratch,
+  int rc = mps_kmeans_assign_tc(centers_view, centers_clk, progress, nullptr, x_bf16, n, K, D, K_valid, D_valid,
+                                centers_bf16_scratch,
                                 cnorm_scratch, centers_f32, sync_ctr, assign, dist, 0, stream);
   if (rc) return rc;
   rc = mps_kmeans_accumulate_sorted(x_bf16, assign, dist, n, K, D, sums, counts_batch, sse, sort_scratch, stream);
   if (rc) return rc;
   rc = mps_kmeans_delta_push(centers_view, counts_view, counts_clk, progress, centers_f32, sums, counts_batch, K, D,
-                             alpha, stream);
+                             K_valid, D_valid, alpha, stream);
   if (rc) return rc;
   return mps_clock2(centers_view, centers_clk, counts_view, counts_clk, worker, progress + 1, fold, stream);
 }

@@ -43,6 +43,8 @@ struct Params {
   float* dist;                   // [n] out: ||c||^2 - 2 x.c of the chosen centre (add ||x||^2 for the SSE)
   int64_t n;
   int K;
+  int K_valid;                   // centres [K_valid, K) are padding: zero coordinates, norm 2^127, never chosen
+  int D_valid;                   // the table holds D_valid values per centre (row-major); columns beyond are zero
   MpsClockView clk;              // consistency gate of the centroid table (gated != 0)
   int gated;
   int progress;
@@ -111,12 +113,30 @@ kmeans_assign_tc_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_
   {
     const int64_t gwarp = (static_cast<int64_t>(blockIdx.x) * kThreads + threadIdx.x) >> 5;
     const int64_t nwarps = (static_cast<int64_t>(gridDim.x) * kThreads) >> 5;
+    const int Kv = p.K_valid, Dv = p.D_valid;
     for (int64_t c = gwarp; c < K; c += nwarps) {
       float sq = 0.f;
       for (int d0 = lane * 4; d0 < D; d0 += 128) {
-        float4 v;
-        const int64_t flat = c * D + d0;
-        if (p.has_view) {
+        float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
+        const int64_t flat = c * D + d0;  // position in the padded [K, D] operand
+        if (c >= Kv) {
+          // padding row: stays zero
+        } else if (Dv != D) {
+          // table rows are D_valid long: element-wise, zero beyond the row
+          float t[4] = {0.f, 0.f, 0.f, 0.f};
+          for (int j = 0; j < 4; ++j) {
+            if (d0 + j >= Dv) break;
+            const int64_t tf = c * Dv + d0 + j;
+            if (p.has_view) {
+              const uint32_t kj = p.centers.begin[0] + static_cast<uint32_t>(tf);
+              const int sj = owner_of(p.centers, kj);
+              t[j] = ld_sys(static_cast<const float*>(p.centers.weights[sj]) + (kj - p.centers.begin[sj]));
+            } else {
+              t[j] = p.centers_f32[tf];
+            }
+          }
+          v = make_float4(t[0], t[1], t[2], t[3]);
+        } else if (p.has_view) {
           const uint32_t key = p.centers.begin[0] + static_cast<uint32_t>(flat);
           const int s = owner_of(p.centers, key);
           const float* src = static_cast<const float*>(p.centers.weights[s]) + (key - p.centers.begin[s]);
@@ -147,6 +167,7 @@ kmeans_assign_tc_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_
         if (p.centers_f32_out) *reinterpret_cast<float4*>(p.centers_f32_out + flat) = v;
       }
       sq = warp_sum(sq);
+      if (c >= Kv) sq = 1.7014118346046923e38f;  // 2^127: exact in bf16, larger than any real distance term
       // ||c||^2 = hi + mid + lo in bf16, columns 0..2 of the augmentation block, zeros elsewhere
       const __nv_bfloat16 h = __float2bfloat16_rn(sq);
       const float r1 = sq - __bfloat162float(h);
@@ -390,9 +411,9 @@ static int launch(const Params& p, const void* x, int max_ctas, cudaStream_t st)
 extern "C" {
 
 int mps_kmeans_assign_tc(const MpsTableView* centers_view, const MpsClockView* clk, int progress,
-                         const float* centers_f32, const void* x_bf16, int64_t n, int K, int D,
-                         void* centers_bf16_scratch, float* cnorm_scratch, float* centers_f32_out, int* sync_ctr,
-                         int32_t* assign, float* dist, int max_ctas, void* stream) {
+                         const float* centers_f32, const void* x_bf16, int64_t n, int K, int D, int K_valid,
+                         int D_valid, void* centers_bf16_scratch, float* cnorm_scratch, float* centers_f32_out,
+                         int* sync_ctr, int32_t* assign, float* dist, int max_ctas, void* stream) {
   if (n <= 0) return 0;
   if (K % mps::kmtc::kChunkN != 0 || K <= 0 || K > 8192) return static_cast<int>(cudaErrorInvalidValue);
   mps::kmtc::Params p{};
@@ -411,6 +432,8 @@ int mps_kmeans_assign_tc(const MpsTableView* centers_view, const MpsClockView* c
   p.dist = dist;
   p.n = n;
   p.K = K;
+  p.K_valid = (K_valid > 0 && K_valid <= K) ? K_valid : K;
+  p.D_valid = (D_valid > 0 && D_valid <= D) ? D_valid : D;
   p.gated = (clk != nullptr && centers_view != nullptr) ? 1 : 0;
   if (p.gated) p.clk = *clk;
   p.progress = progress;

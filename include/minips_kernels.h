@@ -308,13 +308,16 @@ int mps_csr_unpack(const uint8_t* row_len, const void* packed_ids, int id_bits, 
  * into the B-operand fill.  x_bf16: [n, D] row-major bf16 points (D = 64 or 128); centres come
  * either from a range-partitioned fp32 table view of K*D keys (row-major, peer loads, optional
  * consistency gate clk/progress) or, when centers_view is NULL, from the local dense array
- * centers_f32.  K must be a multiple of 128.  Scratch: centers_bf16_scratch [K*D] bf16,
+ * centers_f32.  K must be a multiple of 128 and D 64 or 128 (the tcgen05 tile shapes); any other problem
+ * is run PADDED: K_valid real centres (rows [K_valid, K) of the operand are zero with norm 2^127, so
+ * they are never chosen) and D_valid real coordinates per centre (the table / centers_f32 rows are
+ * D_valid long; x carries zeros in columns [D_valid, D)); 0 = no padding.  Scratch: centers_bf16_scratch [K*D] bf16,
  * cnorm_scratch [K] f32, sync_ctr [1] int.  Outputs: assign [n] int32, dist [n] f32 =
  * ||c||^2 - 2 x.c of the chosen centre (add ||x||^2 for the squared distance); optional
  * centers_f32_out [K*D] receives the pulled fp32 centres. */
 int mps_kmeans_assign_tc(const MpsTableView* centers_view, const MpsClockView* clk, int progress,
-                         const float* centers_f32, const void* x_bf16, int64_t n, int K, int D,
-                         void* centers_bf16_scratch, float* cnorm_scratch, float* centers_f32_out,
+                         const float* centers_f32, const void* x_bf16, int64_t n, int K, int D, int K_valid,
+                         int D_valid, void* centers_bf16_scratch, float* cnorm_scratch, float* centers_f32_out,
                          int* sync_ctr, int32_t* assign, float* dist, int max_ctas, void* stream);
 /* CUDA-core kernel of the same operation on the same bf16 inputs (differential reference). */
 int mps_kmeans_assign_ref(const void* x_bf16, const void* centers_bf16, const float* cnorm, int64_t n,
@@ -342,14 +345,16 @@ int mps_kmeans_delta(const float* centers, const float* counts_old, const float*
  * assigned against (centers_f32_out of mps_kmeans_assign_tc).  f32 tables, D % 4 == 0. */
 int mps_kmeans_delta_push(const MpsTableView* centers_view, const MpsTableView* counts_view,
                           const MpsClockView* counts_clk, int progress, const float* centers,
-                          float* sums, float* counts_batch, int K, int D, float alpha, void* stream);
+                          float* sums, float* counts_batch, int K, int D, int K_valid, int D_valid, float alpha,
+                          void* stream);
 /* One whole mini-batch iteration of a worker (kmeans.cpp:216-275) enqueued by a single host call:
  * assign (centre pull fused) -> accumulate (sorted,
      see above) -> delta + push of both tables -> Clock of both tables at
  * progress + 1 (fold: this worker is the last local one to clock, see mps_clock). */
 int mps_kmeans_step(const MpsTableView* centers_view, const MpsClockView* centers_clk,
                     const MpsTableView* counts_view, const MpsClockView* counts_clk, int worker,
-                    int progress, int fold, const void* x_bf16, int64_t n, int K, int D, float alpha,
+                    int progress, int fold, const void* x_bf16, int64_t n, int K, int D, int K_valid, int D_valid,
+                    float alpha,
                     void* centers_bf16_scratch, float* cnorm_scratch, float* centers_f32, int* sync_ctr,
                     int32_t* assign, float* dist, float* sums, float* counts_batch, float* sse,
                     int* sort_scratch, void* stream);

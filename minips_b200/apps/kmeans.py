@@ -15,7 +15,8 @@ import torch
 
 
 def main(argv=None):
-    from ..models.kmeans import INIT_MODES, KMeansTrainer, make_blobs
+    from ..models.kmeans import INIT_MODES, KMeansTrainer, csr_to_points, make_blobs, pad_points, padded_shape
+    from ..ops.sparse import load_libsvm_file
     from ..parallel.engine import Engine
     from ..parallel.types import MLTask, ModelType, WorkerAlloc
     from ..utils.flags import Context, define_kmeans_flags
@@ -28,13 +29,23 @@ def main(argv=None):
     dev = f"cuda:{engine.device}"
     K, D = ctx.get_int32("K"), ctx.get_int32("num_dims")
     assert 0 <= ctx.get_int32("kStaleness") <= 5, "kStaleness in [0,5] (kmeans.cpp:59-70)"
-    if K % 128 or D not in (64, 128):
-        raise SystemExit("device k-means needs K % 128 == 0 and num_dims in {64, 128} (tcgen05 tile shapes); "
-                         "use the host backend (build/bin/kmeans) for other shapes")
+    try:
+        Kp, Dp = padded_shape(K, D)       # any K, num_dims <= 128: run padded on the tcgen05 tile shapes
+    except ValueError as e:
+        raise SystemExit(str(e))
     servers = max(1, ctx.get_int32("num_servers_per_node"))
     engine.start_everything(num_server_threads_per_node=servers)
-    n_local = ctx.get_int32("num_samples")
-    x = make_blobs(n_local, D, K, device=dev, seed=ctx.get_int32("seed") + rank)
+    if ctx.get_string("input"):
+        # libsvm samples (kmeans.cpp:154-160), parsed on the device; every node keeps its contiguous share
+        csr = load_libsvm_file(ctx.get_string("input"), dev)
+        per = csr.n_rows // world
+        csr = csr.rows(rank * per, per if rank < world - 1 else csr.n_rows - rank * per)
+        x = csr_to_points(csr, D)
+        n_local = x.shape[0]
+        print(f"[node {rank}] loaded {n_local} points of {D} dims from {ctx.get_string('input')}", flush=True)
+    else:
+        n_local = ctx.get_int32("num_samples")
+        x = pad_points(make_blobs(n_local, D, K, device=dev, seed=ctx.get_int32("seed") + rank))
     model = ModelType[ctx.get_string("kModelType")]
     t_c = engine.create_table(num_dims=K * D, model_type=model, staleness=ctx.get_int32("kStaleness"))
     t_n = engine.create_table(num_dims=K, model_type=model, staleness=ctx.get_int32("kStaleness"))
@@ -44,7 +55,7 @@ def main(argv=None):
     def init_fn(info):
         tc, tn = info.create_kv_client_table(t_c), info.create_kv_client_table(t_n)
         t0 = time.time()
-        c0 = INIT_MODES[ctx.get_string("kmeans_init_mode")](x, K, seed=ctx.get_int32("seed"))
+        c0 = INIT_MODES[ctx.get_string("kmeans_init_mode")](x[:, :D], K, seed=ctx.get_int32("seed"))
         tc.add_all(c0.reshape(-1).contiguous())
         tc.clock()
         tn.clock()
@@ -64,7 +75,7 @@ def main(argv=None):
 
     def worker(info):
         tc, tn = info.create_kv_client_table(t_c), info.create_kv_client_table(t_n)
-        tr = KMeansTrainer(tc, tn, x, K, alpha=ctx.get_double("alpha") if ctx.get_double("alpha") > 0 else 1.0)
+        tr = KMeansTrainer(tc, tn, x, K, alpha=ctx.get_double("alpha") if ctx.get_double("alpha") > 0 else 1.0, D=D)
         g = torch.Generator().manual_seed(ctx.get_int32("seed") * 100 + info.worker_id)
         starts = torch.randint(0, max(1, n_local - B + 1), (iters,), generator=g).tolist()
         sse = torch.zeros(1, device=dev)
@@ -83,7 +94,7 @@ def main(argv=None):
         print(f"[node {rank} worker {info.worker_id}] Total training time: {(time.time() - t0) * 1e3:.1f} ms")
 
     task = MLTask()
-    task.set_worker_alloc([WorkerAlloc(n.id, 1) for n in engine.nodes])
+    task.set_worker_alloc([WorkerAlloc(n.id, max(1, ctx.get_int32("num_workers_per_node"))) for n in engine.nodes])
     task.set_tables([t_c, t_n])
     task.set_lambda(worker)
     engine.run(task)

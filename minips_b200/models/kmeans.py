@@ -34,12 +34,50 @@ def make_blobs(n: int, d: int, k_true: int, device="cuda", seed: int = 0, spread
     return out
 
 
-class KMeansAssigner:
-    """Scratch + launcher of the tensor-core assignment kernel."""
+def padded_shape(K: int, D: int) -> Tuple[int, int]:
+    """The tcgen05 tile shapes the kernel runs: K rounded up to a multiple of 128, D to 64 or 128."""
+    if D > 128:
+        raise ValueError(f"device k-means holds a point in one 128-wide operand row: num_dims={D} > 128 "
+                         "(use the host backend, build/bin/kmeans)")
+    return (K + 127) // 128 * 128, (64 if D <= 64 else 128)
 
-    def __init__(self, K: int, D: int, device):
+
+def pad_points(x: torch.Tensor, dtype=torch.bfloat16) -> torch.Tensor:
+    """[n, D] points -> [n, Dp] bf16 with zero columns (Dp = 64 or 128)."""
+    n, D = x.shape
+    _, Dp = padded_shape(1, D)
+    if D == Dp and x.dtype == dtype:
+        return x.contiguous()
+    out = torch.zeros(n, Dp, dtype=dtype, device=x.device)
+    out[:, :D] = x.to(dtype)
+    return out
+
+
+def csr_to_points(csr, num_dims: int) -> torch.Tensor:
+    """Densify libsvm samples (reference kmeans.cpp:154-160 keeps them sparse and walks K*D per point;
+    the tensor-core kernel wants rows): [n, Dp] bf16, feature ids outside [0, num_dims) dropped."""
+    n = csr.n_rows
+    _, Dp = padded_shape(1, num_dims)
+    dev = csr.val.device
+    lens = (csr.row_ptr[1:] - csr.row_ptr[:-1])
+    row_of = torch.repeat_interleave(torch.arange(n, device=dev), lens)
+    base = int(csr.row_ptr[0])
+    col = csr.col[base:base + int(lens.sum())].to(torch.int64) & 0xFFFFFFFF
+    val = csr.val[base:base + int(lens.sum())]
+    keep = col < num_dims
+    out = torch.zeros(n, Dp, dtype=torch.float32, device=dev)
+    out.index_put_((row_of[keep], col[keep]), val[keep], accumulate=True)
+    return out.to(torch.bfloat16)
+
+
+class KMeansAssigner:
+    """Scratch + launcher of the tensor-core assignment kernel.  K / D are the operand (padded) shape;
+    K_valid / D_valid the real problem inside it (see padded_shape)."""
+
+    def __init__(self, K: int, D: int, device, K_valid: int = 0, D_valid: int = 0):
         assert K % 128 == 0 and D in (64, 128), "tcgen05 path: K multiple of 128, D in {64, 128}"
         self.K, self.D, self.dev = K, D, device
+        self.Kv, self.Dv = (K_valid or K), (D_valid or D)
         self.lib = _lib.load()
         # B-operand scratch: [K, D] bf16(-2c) | [K, 64] ||c||^2 as a 3-way bf16 split | [128, 64] ones
         self.c_bf16 = torch.empty(K * D + K * 64 + 128 * 64, dtype=torch.bfloat16, device=device)
@@ -62,14 +100,14 @@ class KMeansAssigner:
         cptr = None
         if client is not None:
             t = client.table
-            assert t.num_keys == self.K * self.D and t.k == 1 and t.dtype == torch.float32
+            assert t.num_keys == self.Kv * self.Dv and t.k == 1 and t.dtype == torch.float32
             client._local_gate()
             view, clk, progress = C.byref(t.view), C.byref(t.clock_view()), client.progress
         else:
-            assert centers is not None and centers.dtype == torch.float32 and centers.numel() == self.K * self.D
+            assert centers is not None and centers.dtype == torch.float32 and centers.numel() == self.Kv * self.Dv
             cptr = C.c_void_p(centers.data_ptr())
         _lib.check(self.lib.mps_kmeans_assign_tc(
-            view, clk, progress, cptr, C.c_void_p(x.data_ptr()), n, self.K, self.D,
+            view, clk, progress, cptr, C.c_void_p(x.data_ptr()), n, self.K, self.D, self.Kv, self.Dv,
             C.c_void_p(self.c_bf16.data_ptr()), C.c_void_p(self.cnorm.data_ptr()), C.c_void_p(self.c_f32.data_ptr()),
             C.c_void_p(self.sync.data_ptr()), C.c_void_p(assign.data_ptr()), C.c_void_p(dist.data_ptr()), max_ctas,
             _lib.stream_ptr(stream)), "kmeans_assign_tc")
@@ -88,22 +126,27 @@ class KMeansAssigner:
 
 
 class KMeansTrainer:
-    """One worker's view of the two tables + its local points."""
+    """One worker's view of the two tables + its local points.  K clusters of D coordinates, any K and any
+    D <= 128 (reference defaults: K=5, num_dims=123, scripts/kmeans.py:17-43): the tables hold exactly K*D and
+    K keys; the kernels run the padded operand shape.  x: [n, Dp] bf16 (pad_points / csr_to_points)."""
 
     def __init__(self, centers_client: KVClientTable, counts_client: KVClientTable, x: torch.Tensor, K: int,
-                 alpha: float = 1.0):
+                 alpha: float = 1.0, D: Optional[int] = None):
         self.tc, self.tn = centers_client, counts_client
         self.x = x
-        self.K, self.D = K, x.shape[1]
+        self.Kv, self.Dv = K, (D if D is not None else x.shape[1])
+        self.K, self.D = padded_shape(self.Kv, self.Dv)
+        assert x.shape[1] == self.D, f"points must be padded to {self.D} columns (pad_points)"
         self.alpha = float(alpha)
         self.dev = centers_client.dev
         self.lib = centers_client.lib
-        self.assigner = KMeansAssigner(K, self.D, self.dev)
+        K, D = self.K, self.D
+        self.assigner = KMeansAssigner(K, D, self.dev, self.Kv, self.Dv)
         self.sums = torch.zeros(K * self.D, dtype=torch.float32, device=self.dev)
         self.cnt = torch.zeros(K, dtype=torch.float32, device=self.dev)
         self.delta_c = torch.empty(K * self.D, dtype=torch.float32, device=self.dev)
         self.delta_n = torch.empty(K, dtype=torch.float32, device=self.dev)
-        self.counts_old = torch.empty(K, dtype=torch.float32, device=self.dev)
+        self.counts_old = torch.zeros(K, dtype=torch.float32, device=self.dev)
         self._out = None
         self._scratch = None
         self.allow_fused = True      # False forces the call-by-call path (tests, debugging)
@@ -122,7 +165,7 @@ class KMeansTrainer:
             return self._step_fused(xb, n, sse)
         # generic path (several local workers share the tables, or non-f32 tables):
         # Get of both tables: counts as a slab pull, centres inside the GEMM kernel
-        self.tn.get_all(out=self.counts_old)
+        self.tn.get_all(out=self.counts_old[:self.Kv])
         assign, dist = self.assigner.assign(xb, client=self.tc, out=self._out)
         self.sums.zero_()
         self.cnt.zero_()
@@ -135,10 +178,14 @@ class KMeansTrainer:
             C.c_void_p(self.assigner.c_f32.data_ptr()), C.c_void_p(self.counts_old.data_ptr()),
             C.c_void_p(self.sums.data_ptr()), C.c_void_p(self.cnt.data_ptr()), self.K, self.D, self.alpha,
             C.c_void_p(self.delta_c.data_ptr()), C.c_void_p(self.delta_n.data_ptr()), sp), "kmeans_delta")
-        # Add + Clock on both tables (kmeans.cpp:269-274)
-        self.tc.add_all(self.delta_c)
+        # Add + Clock on both tables (kmeans.cpp:269-274); the tables hold the real K x D only
+        if (self.Kv, self.Dv) != (self.K, self.D):
+            self.tc.add_all(self.delta_c.view(self.K, self.D)[:self.Kv, :self.Dv].contiguous().view(-1))
+            self.tn.add_all(self.delta_n[:self.Kv].contiguous())
+        else:
+            self.tc.add_all(self.delta_c)
+            self.tn.add_all(self.delta_n)
         self.tc.clock()
-        self.tn.add_all(self.delta_n)
         self.tn.clock()
         return sse
 
@@ -151,8 +198,7 @@ class KMeansTrainer:
 
     def _fusable(self) -> bool:
         tc, tn = self.tc.table, self.tn.table
-        return (self.allow_fused and len(tc.local_workers) <= 1 and len(tn.local_workers) <= 1
-                and tc.dtype == torch.float32
+        return (self.allow_fused and tc.dtype == torch.float32
                 and tn.dtype == torch.float32 and tc.hview is None and tn.hview is None
                 and tc.model_type == tn.model_type and self.tc.progress == self.tn.progress
                 and self.tc.stream is self.tn.stream)
@@ -165,13 +211,28 @@ class KMeansTrainer:
         a = self.assigner
         assign, dist = self._out
         progress = self.tc.progress
-        fold = int(tc.model_type == ModelType.BSP)        # the kernel skips the fold where a rank owns no shard
         s = self.tc.stream or torch.cuda.current_stream()
+        # several workers on this GPU: their clocks this step depends on are ordered on my stream by
+        # events, never waited for inside a kernel (kernels of different streams need not co-run)
+        self.tc._local_gate()
+        self.tn._local_gate()
         with tc.lock, tn.lock:
+            # who folds (BSP): the last local worker to clock, decided and published atomically like
+            # KVClientTable.clock; it waits for the other local workers' adds of this clock
+            fold = 0
+            if tc.model_type == ModelType.BSP:
+                others = [w for w in tc.local_workers if w != self.tc.worker_id]
+                if all(tc.local_clock[w] >= progress + 1 for w in others):
+                    fold = 1
+                    for t in (tc, tn):
+                        for w in others:
+                            if w in t.local_events:
+                                s.wait_event(t.local_events[w])
             _lib.check(self.lib.mps_kmeans_step(
                 C.byref(tc.view), C.byref(tc.clock_view()), C.byref(tn.view), C.byref(tn.clock_view()),
-                self.tc.worker_id, progress, fold, C.c_void_p(xb.data_ptr()), n, self.K, self.D, self.alpha,
-                C.c_void_p(a.c_bf16.data_ptr()), C.c_void_p(a.cnorm.data_ptr()), C.c_void_p(a.c_f32.data_ptr()),
+                self.tc.worker_id, progress, fold, C.c_void_p(xb.data_ptr()), n, self.K, self.D, self.Kv, self.Dv,
+                self.alpha, C.c_void_p(a.c_bf16.data_ptr()), C.c_void_p(a.cnorm.data_ptr()),
+                C.c_void_p(a.c_f32.data_ptr()),
                 C.c_void_p(a.sync.data_ptr()), C.c_void_p(assign.data_ptr()), C.c_void_p(dist.data_ptr()),
                 C.c_void_p(self.sums.data_ptr()), C.c_void_p(self.cnt.data_ptr()), C.c_void_p(sse.data_ptr()),
                 C.c_void_p(self._sort_scratch(n).data_ptr()), self.tc._sp()), "kmeans_step")
@@ -180,6 +241,7 @@ class KMeansTrainer:
             for t, cl in ((tc, self.tc), (tn, self.tn)):
                 t.local_clock[cl.worker_id] = progress + 1
                 t.local_events[cl.worker_id] = ev
+                t.write_epoch += 1
                 if fold and t.own_count > 0:
                     t.fold_clock = progress + 1
                 t.lock.notify_all()

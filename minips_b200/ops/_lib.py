@@ -172,17 +172,18 @@ def _declare(lib):
         "mps_hash_add": ([P(HashView), vp, vp, i64, vp, vp], i32),
         "mps_hash_get": ([P(HashView), P(ClockView), i32, vp, vp, i64, vp], i32),
         "mps_hash_export": ([vp, vp, i64, vp, vp, vp, vp], i32),
-        "mps_kmeans_assign_tc": ([P(TableView), P(ClockView), i32, vp, vp, i64, i32, i32, vp, vp, vp, vp, vp, vp,
-                                  i32, vp], i32),
+        "mps_kmeans_assign_tc": ([P(TableView), P(ClockView), i32, vp, vp, i64, i32, i32, i32, i32, vp, vp, vp, vp, vp,
+                                  vp, i32, vp], i32),
         "mps_dense_lr_forward_tc": ([P(TableView), P(ClockView), i32, vp, vp, vp, i64, i32, f32, vp, vp, vp, vp, vp,
                                      i32, vp], i32),
         "mps_dense_lr_grad": ([vp, vp, i64, i32, vp, vp], i32),
         "mps_kmeans_assign_ref": ([vp, vp, vp, i64, i32, i32, vp, vp, vp], i32),
         "mps_kmeans_accumulate": ([vp, vp, vp, i64, i32, i32, vp, vp, vp, vp], i32),
         "mps_kmeans_delta": ([vp, vp, vp, vp, i32, i32, f32, vp, vp, vp], i32),
-        "mps_kmeans_delta_push": ([P(TableView), P(TableView), P(ClockView), i32, vp, vp, vp, i32, i32, f32, vp], i32),
+        "mps_kmeans_delta_push": ([P(TableView), P(TableView), P(ClockView), i32, vp, vp, vp, i32, i32, i32, i32, f32,
+                                   vp], i32),
         "mps_kmeans_step": ([P(TableView), P(ClockView), P(TableView), P(ClockView), i32, i32, i32, vp, i64, i32, i32,
-                             f32, vp, vp, vp, vp, vp, vp, vp, vp, vp, vp, vp], i32),
+                             i32, i32, f32, vp, vp, vp, vp, vp, vp, vp, vp, vp, vp, vp], i32),
         "mps_kmeans_accumulate_sorted": ([vp, vp, vp, i64, i32, i32, vp, vp, vp, vp, vp], i32),
     }
     for name, (argtypes, restype) in sig.items():

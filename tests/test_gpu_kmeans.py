@@ -169,3 +169,132 @@ def test_sorted_accumulate_matches_oracle(D):
     perm = scratch[3 * K + 1:3 * K + 1 + n].long()
     assert torch.equal(torch.sort(perm).values, torch.arange(n, device="cuda"))
     assert bool((assign[perm][1:] >= assign[perm][:-1]).all())
+
+
+@pytest.mark.parametrize("fused", [True, False])
+@pytest.mark.parametrize("K,D", [(5, 123), (37, 20), (130, 64)])
+def test_kmeans_reference_shapes(K, D, fused):
+    """Any K and any num_dims <= 128 (the reference's own defaults are K=5, num_dims=123,
+    scripts/kmeans.py:17-43): the tables hold exactly K*D and K keys, the tcgen05 kernel runs the
+    problem padded (dummy centres with norm 2^127, zero columns)."""
+    from minips_b200.models.kmeans import (KMeansTrainer, _min_sqdist, init_random, make_blobs, oracle_step,
+                                           pad_points, padded_shape)
+    from minips_b200.parallel.engine import Engine
+    n, batch, iters, alpha = 12_288, 4096, 3, 1.0
+    node = Node(0, "localhost", 0)
+    engine = Engine(node, [node], device=0)
+    engine.start_everything(num_server_threads_per_node=3)
+    try:
+        x = make_blobs(n, D, K, seed=3, spread=0.05)              # [n, D] bf16, unpadded
+        xp = pad_points(x)
+        assert xp.shape[1] == padded_shape(K, D)[1]
+        t_c = engine.create_table(num_dims=K * D, model_type=ModelType.BSP)
+        t_n = engine.create_table(num_dims=K, model_type=ModelType.BSP)
+        c0 = init_random(x, K, seed=1)
+        out = {}
+
+        def fn(info):
+            tc, tn = info.create_kv_client_table(t_c), info.create_kv_client_table(t_n)
+            tc.add_all(c0.reshape(-1).contiguous())
+            tc.clock()
+            tn.clock()
+            tr = KMeansTrainer(tc, tn, xp, K, alpha, D=D)
+            tr.allow_fused = fused
+            sses = [tr.step(i * batch, batch).clone() for i in range(iters)]
+            out["centers"] = tc.get_all().view(K, D)
+            out["counts"] = tn.get_all()
+            out["sse"] = torch.cat(sses).cpu()
+            out["assign_max"] = int(tr._out[0].max())
+
+        task = MLTask()
+        task.set_worker_alloc([WorkerAlloc(0, 1)])
+        task.set_tables([t_c, t_n])
+        task.set_lambda(fn)
+        engine.run(task)
+    finally:
+        engine.stop_everything()
+    assert out["assign_max"] < K, "a padding centre was chosen"
+    c, cnt = c0.clone(), torch.zeros(K, device="cuda")
+    ref_sse = []
+    for i in range(iters):
+        c, cnt, s = oracle_step(c, cnt, [x[i * batch:(i + 1) * batch]], alpha)
+        ref_sse.append(s)
+    assert out["counts"].sum().item() == iters * batch
+    assert abs(out["sse"][0].item() - ref_sse[0]) <= 2e-3 * ref_sse[0] + 1.0
+    cost_dev = _min_sqdist(x, out["centers"]).mean().item()
+    cost_ref = _min_sqdist(x, c).mean().item()
+    assert abs(cost_dev - cost_ref) <= 2e-2 * cost_ref + 1e-3, (cost_dev, cost_ref)
+    assert (out["counts"] - cnt).abs().sum().item() <= 0.05 * iters * batch
+
+
+def test_kmeans_fused_with_two_workers_per_gpu():
+    """Two workers share the GPU (the reference's default layout is 2 workers per node): each keeps the
+    one-call fused step; their BSP dependencies are stream events, the last one to clock folds."""
+    from minips_b200.models.kmeans import KMeansTrainer, _min_sqdist, init_random, make_blobs, oracle_step
+    from minips_b200.parallel.engine import Engine
+    K, D, n, batch, iters, alpha = 128, 64, 32_768, 4096, 3, 1.0
+    node = Node(0, "localhost", 0)
+    engine = Engine(node, [node], device=0)
+    engine.start_everything(num_server_threads_per_node=4)
+    try:
+        x = make_blobs(n, D, K, seed=5, spread=0.05)
+        halves = [x[: n // 2], x[n // 2:]]
+        t_c = engine.create_table(num_dims=K * D, model_type=ModelType.BSP)
+        t_n = engine.create_table(num_dims=K, model_type=ModelType.BSP)
+        c0 = init_random(x, K, seed=1)
+        out = {}
+
+        def fn(info):
+            tc, tn = info.create_kv_client_table(t_c), info.create_kv_client_table(t_n)
+            if info.worker_id == 0:
+                tc.add_all(c0.reshape(-1).contiguous())
+            tc.clock()
+            tn.clock()
+            tr = KMeansTrainer(tc, tn, halves[info.worker_id], K, alpha)
+            assert tr._fusable()
+            for i in range(iters):
+                tr.step(i * batch, batch)
+            if info.worker_id == 0:
+                out["centers"] = tc.get_all().view(K, D).clone()
+                out["counts"] = tn.get_all().clone()
+
+        task = MLTask()
+        task.set_worker_alloc([WorkerAlloc(0, 2)])
+        task.set_tables([t_c, t_n])
+        task.set_lambda(fn)
+        engine.run(task)
+    finally:
+        engine.stop_everything()
+    c, cnt = c0.clone(), torch.zeros(K, device="cuda")
+    for i in range(iters):
+        c, cnt, _ = oracle_step(c, cnt, [h[i * batch:(i + 1) * batch] for h in halves], alpha)
+    assert out["counts"].sum().item() == 2 * iters * batch
+    cost_dev = _min_sqdist(x, out["centers"]).mean().item()
+    cost_ref = _min_sqdist(x, c).mean().item()
+    assert abs(cost_dev - cost_ref) <= 2e-2 * cost_ref + 1e-3, (cost_dev, cost_ref)
+    assert (out["counts"] - cnt).abs().sum().item() <= 0.05 * 2 * iters * batch
+
+
+def test_kmeans_app_on_libsvm_input(tmp_path):
+    """scripts/kmeans.py-style run: libsvm file in, K=5, num_dims=123 (the reference's local defaults)."""
+    import subprocess
+    import sys
+    import os
+    g = torch.Generator().manual_seed(2)
+    rows = []
+    centers = torch.rand(5, 123, generator=g)
+    for i in range(3000):
+        c = centers[i % 5]
+        on = torch.nonzero(torch.rand(123, generator=g) < c * 0.3)[:, 0]
+        rows.append(f"{i % 2} " + " ".join(f"{int(j) + 1}:1" for j in on.tolist()))
+    path = tmp_path / "a9a_like.txt"
+    path.write_text("\n".join(rows) + "\n")
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    p = subprocess.run([sys.executable, "-m", "minips_b200.apps.kmeans", f"--input={path}", "--K=5", "--num_dims=123",
+                        "--batch_size=512", "--num_iters=12", "--kModelType=SSP", "--kStaleness=1",
+                        "--kmeans_init_mode=kmeans++", "--report_interval=4", "--alpha=0.5"],
+                       cwd=root, capture_output=True, text=True, timeout=300)
+    assert p.returncode == 0, p.stdout[-2000:] + p.stderr[-3000:]
+    sse = [float(l.split("SSE/point")[1].split()[0]) for l in p.stdout.splitlines() if "SSE/point" in l]
+    assert len(sse) == 3 and sse[-1] <= sse[0] * 1.05, p.stdout
+    assert "loaded 3000 points" in p.stdout
