@@ -258,6 +258,22 @@ def init_random(x: torch.Tensor, K: int, seed: int = 0) -> torch.Tensor:
 
 
 def _min_sqdist(x: torch.Tensor, centers: torch.Tensor, chunk: int = 1 << 16) -> torch.Tensor:
+    """min_c ||x - c||^2 for every point.  On the device this is the tcgen05 assignment kernel itself
+    (the seeding loops of kmeans_helper.hpp:69-207 are this operation over and over); the PyTorch
+    expression below is the CPU / oversized-K fallback and the oracle."""
+    K, D = centers.shape
+    if x.is_cuda and x.dtype == torch.bfloat16 and D <= 128 and K <= 8192 and x.shape[0] > 0:
+        Kp, Dp = padded_shape(K, D)
+        xp = x if (x.shape[1] == Dp and x.is_contiguous()) else pad_points(x[:, :D])
+        km = KMeansAssigner(Kp, Dp, x.device, K, D)
+        _, dist = km.assign(xp, centers=centers.float().contiguous())
+        xf = xp.float()
+        return (dist + (xf * xf).sum(1)).clamp_min(0)
+    return _min_sqdist_torch(x, centers, chunk)
+
+
+def _min_sqdist_torch(x: torch.Tensor, centers: torch.Tensor, chunk: int = 1 << 16) -> torch.Tensor:
+    """The same quantity in plain PyTorch fp32 (oracle of the tests)."""
     out = torch.empty(x.shape[0], device=x.device)
     cf = centers.float()
     cn = (cf * cf).sum(1)

@@ -152,7 +152,7 @@ def main():
 
     # ---- 7. k-means under BSP: fused step (centre pull in the GEMM kernel, delta + push of both tables in one
     #         kernel) on every rank against the batched oracle over all ranks' batches
-    from minips_b200.models.kmeans import KMeansTrainer, init_random, make_blobs, _min_sqdist
+    from minips_b200.models.kmeans import KMeansTrainer, init_random, make_blobs, _min_sqdist_torch
     from minips_b200.models.kmeans import oracle_step as km_oracle_step
     K7, D7, n7, b7, it7 = 128, 128, 16384, 4096, 3
     xs = [make_blobs(n7, D7, K7, device=dev, seed=50 + r, spread=0.05) for r in range(world)]
@@ -180,7 +180,7 @@ def main():
         c_ref, n_ref, _ = km_oracle_step(c_ref, n_ref, [x[i * b7:(i + 1) * b7] for x in xs], 1.0)
     assert out7["n"].sum().item() == world * it7 * b7, (rank, out7["n"].sum().item())
     allx = torch.cat(xs)
-    cost_dev, cost_ref = _min_sqdist(allx, out7["c"]).mean().item(), _min_sqdist(allx, c_ref).mean().item()
+    cost_dev, cost_ref = _min_sqdist_torch(allx, out7["c"]).mean().item(), _min_sqdist_torch(allx, c_ref).mean().item()
     assert abs(cost_dev - cost_ref) <= 2e-2 * cost_ref + 1e-3, (rank, cost_dev, cost_ref)
     assert (out7["n"] - n_ref).abs().sum().item() <= 0.05 * world * it7 * b7
 

@@ -105,7 +105,7 @@ def test_kmeans_training_matches_oracle(model, fused):
     for i in range(iters):
         c, cnt, s = oracle_step(c, cnt, [x[i * batch:(i + 1) * batch]], alpha)
         ref_sse.append(s)
-    from minips_b200.models.kmeans import _min_sqdist
+    from minips_b200.models.kmeans import _min_sqdist_torch
     assert out["counts"].sum().item() == iters * batch
     # Random seeding puts several centres into the same blob, so exact ties are common and the
     # two implementations may split a blob's points differently: judge by objective.  The first
@@ -114,20 +114,20 @@ def test_kmeans_training_matches_oracle(model, fused):
     for a, b in zip(out["sse"].tolist(), ref_sse):
         assert abs(a - b) <= 1e-2 * abs(b) + 1.0, (a, b)
     assert out["sse"][-1] < out["sse"][0]
-    cost_dev = _min_sqdist(x, out["centers"]).mean().item()
-    cost_ref = _min_sqdist(x, c).mean().item()
+    cost_dev = _min_sqdist_torch(x, out["centers"]).mean().item()
+    cost_ref = _min_sqdist_torch(x, c).mean().item()
     assert abs(cost_dev - cost_ref) <= 2e-2 * cost_ref + 1e-3, (cost_dev, cost_ref)
     assert (out["counts"] - cnt).abs().sum().item() <= 0.05 * iters * batch
 
 
 def test_init_modes_cover_blobs():
-    from minips_b200.models.kmeans import INIT_MODES, _min_sqdist, make_blobs
+    from minips_b200.models.kmeans import INIT_MODES, _min_sqdist_torch, make_blobs
     x = make_blobs(20_000, 64, 16, seed=9, spread=0.05)
     base = None
     for name, fn in INIT_MODES.items():
         c = fn(x, 16, seed=2)
         assert c.shape == (16, 64)
-        cost = _min_sqdist(x, c).mean().item()
+        cost = _min_sqdist_torch(x, c).mean().item()
         if name == "random":
             base = cost
         else:
@@ -177,7 +177,7 @@ def test_kmeans_reference_shapes(K, D, fused):
     """Any K and any num_dims <= 128 (the reference's own defaults are K=5, num_dims=123,
     scripts/kmeans.py:17-43): the tables hold exactly K*D and K keys, the tcgen05 kernel runs the
     problem padded (dummy centres with norm 2^127, zero columns)."""
-    from minips_b200.models.kmeans import (KMeansTrainer, _min_sqdist, init_random, make_blobs, oracle_step,
+    from minips_b200.models.kmeans import (KMeansTrainer, _min_sqdist_torch, init_random, make_blobs, oracle_step,
                                            pad_points, padded_shape)
     from minips_b200.parallel.engine import Engine
     n, batch, iters, alpha = 12_288, 4096, 3, 1.0
@@ -221,8 +221,8 @@ def test_kmeans_reference_shapes(K, D, fused):
         ref_sse.append(s)
     assert out["counts"].sum().item() == iters * batch
     assert abs(out["sse"][0].item() - ref_sse[0]) <= 2e-3 * ref_sse[0] + 1.0
-    cost_dev = _min_sqdist(x, out["centers"]).mean().item()
-    cost_ref = _min_sqdist(x, c).mean().item()
+    cost_dev = _min_sqdist_torch(x, out["centers"]).mean().item()
+    cost_ref = _min_sqdist_torch(x, c).mean().item()
     assert abs(cost_dev - cost_ref) <= 2e-2 * cost_ref + 1e-3, (cost_dev, cost_ref)
     assert (out["counts"] - cnt).abs().sum().item() <= 0.05 * iters * batch
 
@@ -230,7 +230,7 @@ def test_kmeans_reference_shapes(K, D, fused):
 def test_kmeans_fused_with_two_workers_per_gpu():
     """Two workers share the GPU (the reference's default layout is 2 workers per node): each keeps the
     one-call fused step; their BSP dependencies are stream events, the last one to clock folds."""
-    from minips_b200.models.kmeans import KMeansTrainer, _min_sqdist, init_random, make_blobs, oracle_step
+    from minips_b200.models.kmeans import KMeansTrainer, _min_sqdist_torch, init_random, make_blobs, oracle_step
     from minips_b200.parallel.engine import Engine
     K, D, n, batch, iters, alpha = 128, 64, 32_768, 4096, 3, 1.0
     node = Node(0, "localhost", 0)
@@ -269,8 +269,8 @@ def test_kmeans_fused_with_two_workers_per_gpu():
     for i in range(iters):
         c, cnt, _ = oracle_step(c, cnt, [h[i * batch:(i + 1) * batch] for h in halves], alpha)
     assert out["counts"].sum().item() == 2 * iters * batch
-    cost_dev = _min_sqdist(x, out["centers"]).mean().item()
-    cost_ref = _min_sqdist(x, c).mean().item()
+    cost_dev = _min_sqdist_torch(x, out["centers"]).mean().item()
+    cost_ref = _min_sqdist_torch(x, c).mean().item()
     assert abs(cost_dev - cost_ref) <= 2e-2 * cost_ref + 1e-3, (cost_dev, cost_ref)
     assert (out["counts"] - cnt).abs().sum().item() <= 0.05 * 2 * iters * batch
 
