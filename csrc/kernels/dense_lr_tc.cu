@@ -267,4 +267,8 @@ int mps_dense_lr_grad(const void* x_bf16, const float* coef, int64_t n, int D, f
   return 0;
 }
 
+/* 1 if an mbarrier wait of a tcgen05 kernel of this file expired since the last call (clears the flag);
+ * synchronises with the device. */
+int mps_dense_lr_tc_error(void) { return mps::tc::tc_take_timeout_flag(); }
+
 }  // extern "C"

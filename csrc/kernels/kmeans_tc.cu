@@ -455,4 +455,8 @@ int mps_kmeans_assign_ref(const void* x_bf16, const void* centers_bf16, const fl
   return 0;
 }
 
+/* 1 if an mbarrier wait of a tcgen05 kernel of this file expired since the last call (clears the flag);
+ * synchronises with the device. */
+int mps_kmeans_tc_error(void) { return mps::tc::tc_take_timeout_flag(); }
+
 }  // extern "C"

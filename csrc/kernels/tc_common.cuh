@@ -37,14 +37,32 @@ __device__ __forceinline__ bool mbar_try_wait(uint64_t* bar, uint32_t parity) {
       : "memory");
   return ok != 0;
 }
-// try_wait suspends in hardware for a bounded time; the loop re-arms it.  A (generous) clock
-// budget turns a protocol bug into a trap with an error code instead of a hung GPU.
+// try_wait suspends in hardware for a bounded time; the loop re-arms it.  A (generous) clock budget
+// turns a protocol bug into an ERROR FLAG instead of a hung GPU or a trap (a trap would take the CUDA
+// context — and every table in it — down): the first wait that expires raises g_tc_timeout, every
+// later wait of the launch falls through at once, the kernel drains with garbage results, and the
+// host reports the flag where it reports the tables' own time-outs (mps_tc_error, DeviceTable.check_error).
+static __device__ int g_tc_timeout = 0;  // one copy per translation unit that includes this header
 __device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
   if (mbar_try_wait(bar, parity)) return;
   const long long t0 = clock64();
   while (!mbar_try_wait(bar, parity)) {
-    if (clock64() - t0 > 20000000000LL) __trap();
+    if (*reinterpret_cast<volatile int*>(&g_tc_timeout)) return;
+    if (clock64() - t0 > 20000000000LL) {
+      atomicExch(&g_tc_timeout, 1);
+      return;
+    }
   }
+}
+// host side: read and clear this translation unit's flag
+static inline int tc_take_timeout_flag() {
+  int v = 0;
+  if (cudaMemcpyFromSymbol(&v, g_tc_timeout, sizeof(int)) != cudaSuccess) return -1;
+  if (v) {
+    const int zero = 0;
+    cudaMemcpyToSymbol(g_tc_timeout, &zero, sizeof(int));
+  }
+  return v;
 }
 __device__ __forceinline__ void fence_barrier_init() {
   asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");

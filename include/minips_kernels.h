@@ -319,6 +319,10 @@ int mps_kmeans_assign_tc(const MpsTableView* centers_view, const MpsClockView* c
                          const float* centers_f32, const void* x_bf16, int64_t n, int K, int D, int K_valid,
                          int D_valid, void* centers_bf16_scratch, float* cnorm_scratch, float* centers_f32_out,
                          int* sync_ctr, int32_t* assign, float* dist, int max_ctas, void* stream);
+/* The tcgen05 kernels bound every mbarrier wait; one that expires (a protocol bug, never seen in the
+ * tests) raises a flag instead of trapping the context.  These read and clear it (device sync). */
+int mps_kmeans_tc_error(void);
+int mps_dense_lr_tc_error(void);
 /* CUDA-core kernel of the same operation on the same bf16 inputs (differential reference). */
 int mps_kmeans_assign_ref(const void* x_bf16, const void* centers_bf16, const float* cnorm, int64_t n,
                           int K, int D, int32_t* assign, float* dist, void* stream);

@@ -218,6 +218,9 @@ class DeviceTable:
         if self.hview is not None and int(self.overflow.item()) != 0:
             raise RuntimeError(f"table {self.table_id}: a hash shard overflowed (capacity {self.hash_capacity}); "
                                "create the table with a larger map_capacity")
+        if self.lib.mps_kmeans_tc_error() > 0 or self.lib.mps_dense_lr_tc_error() > 0:
+            raise RuntimeError("a tcgen05 kernel's mbarrier wait expired (pipeline protocol error); its results "
+                               "are invalid")
         if int(self.pad_tensor()[_lib.PAD_ERROR].item()) != 0:
             raise RuntimeError(f"table {self.table_id}: device-side wait timed out "
                                f"(a peer did not reach the expected clock within {self._timeout_s}s)")
