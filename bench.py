@@ -170,6 +170,12 @@ def measure_lr(engine, args, data, dtype_name, want_e2e, want_timeline=False):
             result["e2e_launches_per_step"] = loader.launches_per_batch + 1
             result["e2e_loss_last"] = float(hl[-1, 0]) / B
         result["clocks"] = sampler.stop()
+        if want_timeline and not dense and getattr(engine.tables[tid], "bucket", None) is not None and rank == 0:
+            t = engine.tables[tid].bucket.timeline.cpu().double()
+            names = ["gate", "bucket", "request+wait", "serve+wait", "compute", "delta+wait", "apply"]
+            print("timeline us (bucketed step, rank 0, CTA 0, last step): " +
+                  ", ".join(f"{n}={v:.1f}" for n, v in zip(names, ((t[1:] - t[:-1]) / 1e3).tolist())),
+                  file=sys.stderr)
         if want_timeline and dense:
             # untimed extra run with the in-kernel phase timeline (rank 0 prints the means)
             n_tl = 60

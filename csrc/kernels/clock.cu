@@ -149,6 +149,7 @@ __global__ void reset_pad_kernel(const __grid_constant__ MpsClockView c, int sta
     for (int i = 0; i < 4; ++i) pad[MPS_PAD_LOCALCTR + i] = 0;
   }
   for (int i = threadIdx.x; i < 4 * MPS_MAX_RANKS; i += blockDim.x) pad[MPS_PAD_XCNT + i] = 0;
+  for (int i = threadIdx.x; i < 8 * MPS_MAX_RANKS; i += blockDim.x) pad[MPS_PAD_BCNT + i] = 0;
 }
 
 }  // namespace mps

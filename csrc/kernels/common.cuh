@@ -199,6 +199,32 @@ __device__ __forceinline__ void cta_gate(const MpsClockView& c, int progress) {
   __syncthreads();
 }
 
+// ---------------------------------------------------------------- per-CTA completion counters
+// "All G CTAs of rank r have finished phase X" without a last-CTA hop: every CTA publishes its own
+// completion behind its own system fence (all CTAs in parallel) by adding 1 to slot `my_rank` of a
+// counter on every rank; a reader that sees the full count has synchronised with every CTA's fence
+// through the chain of reds.
+// all `n` counters at `cnt` reached `target`?  (local spin on this rank's pad)
+__device__ __forceinline__ bool all_reached(const int* cnt, int n, int target) {
+  for (int r = 0; r < n; ++r)
+    if (ld_acquire_sys(cnt + r) < target) return false;
+  return true;
+}
+// this CTA's part is done: system fence, then +1 on slot `me` of the counter on every rank
+__device__ __forceinline__ void cta_signal(const MpsClockView& c, int slot, bool multi) {
+  if (multi) fence_sys(); else __threadfence();
+  for (int i = 0; i < c.num_ranks; ++i) {
+    const int r = (c.my_rank + i) % c.num_ranks;
+    asm volatile("red.relaxed.sys.global.add.s32 [%0], %1;" ::"l"(c.pad[r] + slot + c.my_rank), "r"(1) : "memory");
+  }
+}
+
+__device__ __forceinline__ uint32_t ld_sys_u32(const uint32_t* p) {
+  uint32_t v;
+  asm volatile("ld.relaxed.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+  return v;
+}
+
 __device__ __forceinline__ float warp_sum(float v) {
 #pragma unroll
   for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);

@@ -173,22 +173,6 @@ __device__ __forceinline__ void replica_fill(const MpsTableView& v, int rot_shar
   }
 }
 
-// all `n` counters at `cnt` reached `target`?  (local spin on this rank's pad)
-__device__ __forceinline__ bool all_reached(const int* cnt, int n, int target) {
-  for (int r = 0; r < n; ++r)
-    if (ld_acquire_sys(cnt + r) < target) return false;
-  return true;
-}
-
-// this CTA's part is done: system fence, then +1 on slot `me` of the counter on every rank
-__device__ __forceinline__ void cta_signal(const MpsClockView& c, int slot, bool multi) {
-  if (multi) fence_sys(); else __threadfence();
-  for (int i = 0; i < c.num_ranks; ++i) {
-    const int r = (c.my_rank + i) % c.num_ranks;
-    asm volatile("red.relaxed.sys.global.add.s32 [%0], %1;" ::"l"(c.pad[r] + slot + c.my_rank), "r"(1) : "memory");
-  }
-}
-
 template <int L, typename T, bool kPacked>
 __global__ void __launch_bounds__(512, 2)
 lr_train_xchg_kernel(const __grid_constant__ MpsTableView v, const __grid_constant__ MpsClockView c,

@@ -33,6 +33,8 @@ extern "C" {
 #define MPS_PAD_LOCALCTR (MPS_PAD_MINCLOCK + 1)              /* [4] local CTA-completion counters */
 /* LR exchange kernel: [2 sets][ready | arrived][MPS_MAX_RANKS] = CTAs of rank r that are done */
 #define MPS_PAD_XCNT (MPS_PAD_LOCALCTR + 4)
+/* bucketed sparse LR step: [2 sets][request | reply | delta | applied][MPS_MAX_RANKS] */
+#define MPS_PAD_BCNT (MPS_PAD_XCNT + 4 * MPS_MAX_RANKS)
 #define MPS_PAD_INTS 1024                                    /* pad size in int32 (4 KiB)         */
 
 enum { MPS_MODEL_SSP = 0, MPS_MODEL_BSP = 1, MPS_MODEL_ASP = 2 }; /* driver/engine.hpp:25-27 */
@@ -157,6 +159,35 @@ enum { MPS_CSR_PLAIN = 0, MPS_CSR_PACKED = 1 };
 int mps_lr_step_sparse(const MpsTableView* view, const MpsClockView* clk, int worker, int progress,
                        const MpsCsr* csr, int64_t row_begin, int64_t batch, double alpha,
                        float* loss_out, void* stream);
+
+/* The same iteration as a request / reply / delta message flow between the GPUs (csrc/kernels/
+ * lr_bucket.cu; the shape of the reference's kGet / kAdd traffic, worker/kv_client_table.hpp:168-195):
+ * feature ids bucketed per owner, buckets shipped as contiguous peer stores, owners gather / apply in
+ * their own HBM.  NVLink carries 3 x 4 bytes (fp32) per non-zero in long bursts instead of two
+ * scattered small packets.  `bucket` describes the scratch: base[r] = rank r's symmetric scratch
+ * (inbox_keys [R][cap] u32 | inbox_delta [R][cap] T | inbox_meta [R][2] i64 | reply [cap] T at the
+ * given byte offsets), plus local buffers send_keys / slot [cap] u32, delta_send [cap] T, hist
+ * [MPS_MAX_RANKS] u64; cap >= non-zeros of any batch; seq = number of bucketed launches on this table
+ * so far (the same on every rank).  Collective: every rank runs exactly one worker through it, step by
+ * step, with the same grid; batches must not wrap.  The Clock is part of the kernel: when it ends, every
+ * rank's pad says that every worker reached progress + 1 and every shard is folded there (no mps_clock
+ * afterwards).  gated != 0: wait for the table's Get gate of `progress` first (needed only when the
+ * previous clock of the table was published by the generic path). */
+typedef struct MpsBucket {
+  void* base[MPS_MAX_RANKS];
+  int64_t off_inbox_keys, off_inbox_delta, off_inbox_meta, off_reply;
+  int64_t cap;
+  uint32_t* send_keys;
+  uint32_t* slot;
+  void* delta_send;
+  unsigned long long* hist;
+  unsigned long long* timeline; /* NULL or 8 slots: %globaltimer at the phase boundaries (CTA 0) */
+  int32_t seq;
+  int32_t reserved;
+} MpsBucket;
+int mps_lr_step_bucketed(const MpsTableView* view, const MpsClockView* clk, int gated, int progress,
+                         const MpsCsr* csr, int64_t row_begin, int64_t batch, double alpha,
+                         const MpsBucket* bucket, float* loss_out, int avg_nnz, void* stream);
 
 /* Dense regime, persistent cooperative kernel running `n_iters` whole iterations
  * (Get -> SpMV -> grad -> Add -> Clock [-> BSP fold]) without returning to the host:

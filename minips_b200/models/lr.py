@@ -122,6 +122,47 @@ class XchgScratch:
         self.buf.close()
 
 
+class BucketScratch:
+    """Scratch of the bucketed (message-flow) sparse step, csrc/kernels/lr_bucket.cu: per rank an inbox for
+    the keys and deltas of every requester, a reply buffer for its own requests (all peer-mapped) and local
+    staging.  cap = the largest number of non-zeros a batch can have.  Creating it is collective."""
+
+    def __init__(self, table: DeviceTable, cap: int):
+        import os
+        from ..parallel.heap import SymmetricBuffer
+        R, it = table.world, table.itemsize
+        self.cap = cap = (int(cap) + 63) // 64 * 64
+        a256 = lambda n: (n + 255) // 256 * 256  # noqa: E731
+        off_keys = 0
+        off_delta = off_keys + a256(R * cap * 4)
+        off_meta = off_delta + a256(R * cap * it)
+        off_reply = off_meta + a256(R * 2 * 8)
+        total = off_reply + a256(cap * it)
+        self.buf = SymmetricBuffer(total, table.control, table.device)
+        dev = f"cuda:{table.device}"
+        self.send_keys = torch.empty(cap, dtype=torch.int32, device=dev)
+        self.slot = torch.empty(cap, dtype=torch.int32, device=dev)
+        self.delta_send = torch.empty(cap, dtype=table.dtype, device=dev)
+        self.hist = torch.zeros(_lib.MAX_RANKS, dtype=torch.int64, device=dev)
+        self.timeline = torch.zeros(8, dtype=torch.int64, device=dev)
+        b = _lib.Bucket()
+        for r in range(R):
+            b.base[r] = self.buf.ptrs[r]
+        b.off_inbox_keys, b.off_inbox_delta, b.off_inbox_meta, b.off_reply = off_keys, off_delta, off_meta, off_reply
+        b.cap = cap
+        b.send_keys = self.send_keys.data_ptr()
+        b.slot = self.slot.data_ptr()
+        b.delta_send = self.delta_send.data_ptr()
+        b.hist = self.hist.data_ptr()
+        b.timeline = self.timeline.data_ptr() if os.environ.get("MINIPS_BUCKET_TIMELINE") == "1" else None
+        self.c = b
+        self.launch_seq = 0
+        self.last_epoch = -1        # table.write_epoch right after the last bucketed step
+
+    def close(self):
+        self.buf.close()
+
+
 class SparseLRTrainer:
     """Device trainer bound to one worker's KVClientTable (fp32 or fp64 tables; the reference's
     tables are Val = double, lr_example.cpp:182)."""
@@ -136,6 +177,8 @@ class SparseLRTrainer:
         self._replica: Optional[torch.Tensor] = None
         self._gacc: Optional[torch.Tensor] = None
         self.avg_nnz = max(1, int(round(data.nnz / max(1, data.n_rows))))
+        self._max_batch_nnz = -1
+        self._bucket_batch = 0
         assert self.table.dtype in (torch.float32, torch.float64) and self.table.k == 1
 
     def _scratch(self):
@@ -156,6 +199,22 @@ class SparseLRTrainer:
         t = self.table
         return (t.model_type == ModelType.BSP and t.num_workers == t.world and len(t.local_workers) == 1
                 and t.hview is None)
+
+    def bucket_ok(self) -> bool:
+        """The message-flow step needs every rank of the table to run exactly one worker through it, step by
+        step (any consistency model: it is BSP-tight, which satisfies the looser ones).  On one GPU every
+        access is local already and the per-non-zero kernel is the right one."""
+        t = self.table
+        return (t.world > 1 and t.num_workers == t.world and len(t.local_workers) == 1 and t.hview is None
+                and t.num_shards % t.world == 0)
+
+    def _bucket(self) -> BucketScratch:
+        t = self.table
+        if getattr(t, "bucket", None) is None:
+            # collective: every rank reaches its first bucketed step together; all agree on the capacity
+            cap = max(t.control.all_gather(self._max_batch_nnz))
+            t.bucket = BucketScratch(t, cap)
+        return t.bucket
 
     def _xchg(self) -> XchgScratch:
         t = self.table
@@ -244,8 +303,11 @@ class SparseLRTrainer:
         return host_loss
 
     @traced("lr.step_sparse")
-    def step_sparse(self, row_begin: int, batch: int, loss: Optional[torch.Tensor] = None) -> torch.Tensor:
-        """One iteration in the sparse regime: fused pull+forward+grad+push kernel, then Clock."""
+    def step_sparse(self, row_begin: int, batch: int, loss: Optional[torch.Tensor] = None,
+                    protocol: str = "auto") -> torch.Tensor:
+        """One iteration in the sparse regime, then Clock.  protocol "bucket": keys, values and deltas travel
+        between the GPUs as per-owner messages (lr_bucket.cu); "pernnz": one peer ld / red per non-zero
+        (lr.cu); "auto" = bucket whenever it applies (several GPUs, one worker per rank, lockstep)."""
         c = self.client
         t = self.table
         if loss is None:
@@ -253,9 +315,38 @@ class SparseLRTrainer:
         cv = t.clock_view()
         csr = self.data.c_struct()
         c._local_gate()
-        _lib.check(self.lib.mps_lr_step_sparse(
-            C.byref(t.view), C.byref(cv), c.worker_id, c.progress, C.byref(csr), row_begin, batch,
-            self.alpha, C.c_void_p(loss.data_ptr()), c._sp()), "lr_step_sparse")
+        wraps = row_begin + batch > self.data.n_rows
+        use_bucket = protocol == "bucket" or (protocol == "auto" and self.bucket_ok() and not wraps)
+        if use_bucket:
+            assert self.bucket_ok() and not wraps, "bucket protocol: several ranks, one worker each, no wrap-around"
+            if self._max_batch_nnz < 0:
+                rp = self.data.row_ptr
+                self._max_batch_nnz = int((rp[batch:] - rp[:-batch]).max().item()) if self.data.n_rows > batch \
+                    else self.data.nnz
+                self._bucket_batch = batch
+            assert batch <= self._bucket_batch, "bucket scratch was sized for a smaller batch"
+            bk = self._bucket()
+            bk.c.seq = bk.launch_seq
+            bk.launch_seq += 1
+            gated = int(bk.last_epoch != t.write_epoch)       # previous clock came from the generic path
+            _lib.check(self.lib.mps_lr_step_bucketed(
+                C.byref(t.view), C.byref(cv), gated, c.progress, C.byref(csr), row_begin, batch, self.alpha,
+                C.byref(bk.c), C.c_void_p(loss.data_ptr()), self.avg_nnz, c._sp()), "lr_step_bucketed")
+            t.write_epoch += 1
+            bk.last_epoch = t.write_epoch
+            with t.lock:                                      # host mirror of the clock the kernel published
+                c.progress += 1
+                t.local_clock[c.worker_id] = c.progress
+                ev = torch.cuda.Event()
+                ev.record(c.stream or torch.cuda.current_stream())
+                t.local_events[c.worker_id] = ev
+                t.fold_clock = c.progress
+                t.lock.notify_all()
+            return loss
+        else:
+            _lib.check(self.lib.mps_lr_step_sparse(
+                C.byref(t.view), C.byref(cv), c.worker_id, c.progress, C.byref(csr), row_begin, batch,
+                self.alpha, C.c_void_p(loss.data_ptr()), c._sp()), "lr_step_sparse")
         t.write_epoch += 1
         c.clock()
         return loss

@@ -90,6 +90,25 @@ class Xchg(C.Structure):
     ]
 
 
+class Bucket(C.Structure):
+    """MpsBucket: scratch of the bucketed (message-flow) sparse LR step."""
+    _fields_ = [
+        ("base", C.c_void_p * MAX_RANKS),
+        ("off_inbox_keys", C.c_int64),
+        ("off_inbox_delta", C.c_int64),
+        ("off_inbox_meta", C.c_int64),
+        ("off_reply", C.c_int64),
+        ("cap", C.c_int64),
+        ("send_keys", C.c_void_p),
+        ("slot", C.c_void_p),
+        ("delta_send", C.c_void_p),
+        ("hist", C.c_void_p),
+        ("timeline", C.c_void_p),
+        ("seq", C.c_int32),
+        ("reserved", C.c_int32),
+    ]
+
+
 class HashView(C.Structure):
     _fields_ = [
         ("keys", C.c_void_p * MAX_SHARDS),
@@ -156,6 +175,8 @@ def _declare(lib):
         "mps_reset_pad": ([P(ClockView), i32, vp], i32),
         "mps_straggle": ([C.c_longlong, vp], i32),
         "mps_lr_step_sparse": ([P(TableView), P(ClockView), i32, i32, P(Csr), i64, i64, f64, vp, vp], i32),
+        "mps_lr_step_bucketed": ([P(TableView), P(ClockView), i32, i32, P(Csr), i64, i64, f64, P(Bucket), vp, i32,
+                                  vp], i32),
         "mps_lr_train_dense": ([P(TableView), P(ClockView), i32, i32, P(Csr), vp, i32, i64, f64, vp, vp, vp,
                                 i32, vp], i32),
         "mps_lr_train_dense_ex": ([P(TableView), P(ClockView), i32, i32, P(Csr), vp, i32, i64, f64, vp, vp, vp,

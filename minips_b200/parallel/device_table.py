@@ -145,6 +145,7 @@ class DeviceTable:
         self.ckpt_barrier = threading.Barrier(1)
         self.write_epoch = 0      # bumped by every local write that bypasses a fused kernel's replica
         self.xchg = None          # symmetric scratch of the LR exchange kernel (models/lr.py), lazily
+        self.bucket = None        # scratch of the bucketed sparse LR step, lazily
 
     # ---- views -------------------------------------------------------------------------
     def clock_view(self) -> _lib.ClockView:
@@ -229,6 +230,9 @@ class DeviceTable:
         if self.xchg is not None:
             self.xchg.close()
             self.xchg = None
+        if self.bucket is not None:
+            self.bucket.close()
+            self.bucket = None
         self.slab.close()
 
     # ---- whole-table helpers (host convenience, not hot path) ----------------------------

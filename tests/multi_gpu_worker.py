@@ -105,17 +105,33 @@ def main():
             assert torch.equal(out["replica"], out["w"]), "every rank's replica is the table"
             multicast = out["mc"]
 
-    # ---- 4. fused LR, sparse per-step kernel, BSP
-    t4 = engine.create_table(num_dims=nd, model_type=ModelType.BSP)
+    # ---- 4. fused LR, sparse regime, BSP: per-non-zero peer accesses and the bucketed message flow, fp32 and
+    #         fp64, all against the same synchronous oracle
+    for dtype, protocol in ((torch.float32, "pernnz"), (torch.float32, "bucket"), (torch.float64, "bucket")):
+        t4 = engine.create_table(num_dims=nd, model_type=ModelType.BSP, dtype=dtype)
 
-    def lr_sparse_fn(info):
-        tr = SparseLRTrainer(info.create_kv_client_table(t4), datas[rank], alpha)
+        def lr_sparse_fn(info, t4=t4, protocol=protocol):
+            tr = SparseLRTrainer(info.create_kv_client_table(t4), datas[rank], alpha)
+            for i in range(iters):
+                tr.step_sparse(int(starts[rank][i]), batch, protocol=protocol)
+            out["ws"] = tr.client.get_all()
+
+        run_task(engine, [t4], lr_sparse_fn)
+        if dtype == torch.float64:
+            torch.testing.assert_close(out["ws"], w64, rtol=1e-9, atol=1e-12)
+        else:
+            torch.testing.assert_close(out["ws"], w, rtol=3e-4, atol=3e-5)
+    # ... and under ASP / SSP the bucketed flow makes progress to a comparable model (it is BSP-tight)
+    t4a = engine.create_table(num_dims=nd, model_type=ModelType.ASP)
+
+    def lr_sparse_asp(info):
+        tr = SparseLRTrainer(info.create_kv_client_table(t4a), datas[rank], alpha)
         for i in range(iters):
             tr.step_sparse(int(starts[rank][i]), batch)
-        out["ws"] = tr.client.get_all()
+        out["wa"] = tr.client.get_all()
 
-    run_task(engine, [t4], lr_sparse_fn)
-    torch.testing.assert_close(out["ws"], w, rtol=3e-4, atol=3e-5)
+    run_task(engine, [t4a], lr_sparse_asp)
+    torch.testing.assert_close(out["wa"], w, rtol=3e-4, atol=3e-5)
 
     # ---- 5. two workers per GPU under BSP (local stream ordering + remote flags)
     t5 = engine.create_table(num_dims=2048, model_type=ModelType.BSP)
