@@ -110,6 +110,36 @@ clock2_kernel(const __grid_constant__ MpsTableView v0, const __grid_constant__ M
   }
 }
 
+// Resident server of a rank that owns BSP shards but runs no worker of the task (the reference's server
+// thread applies the buffered adds at every clock edge, bsp_model.cpp:14-32): loops
+//   wait until every worker clocked past `next`  ->  fold my shards  ->  publish folded = next
+// until the host raises *done (after the workers' ranks reported the end of the task) and no further
+// edge is pending.  No host round trip gates an edge.  Idle waiting is not an error: only the host ends it.
+__global__ void __launch_bounds__(256)
+fold_server_kernel(const __grid_constant__ MpsTableView v, const __grid_constant__ MpsClockView c, int start_clock,
+                   const volatile int* __restrict__ done) {
+  __shared__ int s_go;
+  int next = start_clock + 1;
+  while (true) {
+    if (threadIdx.x == 0) {
+      unsigned ns = 64;
+      while (true) {
+        if (pad_min_clock(c) >= next) { s_go = 1; break; }
+        if (*done != 0 && pad_min_clock(c) < next) { s_go = 0; break; }
+        if (pad_error(c)) { s_go = 0; break; }
+        __nanosleep(ns);
+        if (ns < 2048) ns <<= 1;
+      }
+    }
+    __syncthreads();
+    const int go = s_go;
+    __syncthreads();
+    if (!go) return;
+    clock_body(v, c, -1, next, 1, blockIdx.x, gridDim.x);
+    ++next;
+  }
+}
+
 __global__ void barrier_kernel(const __grid_constant__ MpsClockView c, int epoch) {
   if (threadIdx.x != 0 || blockIdx.x != 0) return;
   fence_sys();
@@ -187,6 +217,27 @@ int mps_clock2(const MpsTableView* view0, const MpsClockView* clk0, const MpsTab
   mps::clock2_kernel<<<dim3(g0 > g1 ? g0 : g1, 2), 256, 0, st>>>(*view0, *clk0, g0, *view1, *clk1, g1, worker,
                                                                   new_clock, fold);
   MPS_LAUNCH_CHECK();
+  return 0;
+}
+
+int mps_fold_server(const MpsTableView* view, const MpsClockView* clk, int start_clock, const int* done_flag,
+                    void* stream) {
+  if (clk->model != MPS_MODEL_BSP || clk->own_count <= 0) return 0;
+  auto st = static_cast<cudaStream_t>(stream);
+  int grid = clock_grid(view, clk, 1);
+  int dev = 0, sms = 148, per_sm = 0;
+  cudaGetDevice(&dev);
+  cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+  MPS_CHECK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, mps::fold_server_kernel, 256, 0));
+  // every CTA must be resident (they wait on the workers together), and the servers of several tables
+  // must fit side by side: at most one 256-thread CTA per SM each
+  if (grid > sms * per_sm) grid = sms * per_sm;
+  if (grid > sms) grid = sms;
+  MpsTableView v = *view;
+  MpsClockView c = *clk;
+  void* args[] = {&v, &c, &start_clock, &done_flag};
+  MPS_CHECK(cudaLaunchCooperativeKernel(reinterpret_cast<void*>(mps::fold_server_kernel), dim3(grid), dim3(256), args,
+                                        0, st));
   return 0;
 }
 

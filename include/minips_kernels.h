@@ -119,6 +119,12 @@ int mps_clock(const MpsTableView* view, const MpsClockView* clk, int worker, int
 /* Clock of two tables of the same worker in one launch (k-means: centres and counts). */
 int mps_clock2(const MpsTableView* view0, const MpsClockView* clk0, const MpsTableView* view1,
                const MpsClockView* clk1, int worker, int new_clock, int fold, void* stream);
+/* Resident fold server for a rank that owns BSP shards of the table but runs no worker of the task: one
+ * persistent launch applies every clock edge after start_clock (wait for all workers, fold staging into
+ * the weights, publish folded) until the host writes a non-zero value to *done_flag (pinned, device-
+ * readable host memory) and no edge is pending.  bsp_model.cpp:14-32 without a host round trip. */
+int mps_fold_server(const MpsTableView* view, const MpsClockView* clk, int start_clock, const int* done_flag,
+                    void* stream);
 /* Device-side barrier over the pads (comm/mailbox.cpp:362-396 semantics). */
 int mps_barrier(const MpsClockView* clk, int epoch, void* stream);
 /* Injected straggler (lr_example.cpp:347-353 sleeps the worker thread): stalls `stream` for ns

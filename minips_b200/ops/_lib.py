@@ -171,6 +171,7 @@ def _declare(lib):
         "mps_pull_dense": ([P(TableView), P(ClockView), i32, i32, vp, vp], i32),
         "mps_push_dense": ([P(TableView), vp, i32, i32, vp], i32),
         "mps_clock": ([P(TableView), P(ClockView), i32, i32, i32, vp], i32),
+        "mps_fold_server": ([P(TableView), P(ClockView), i32, vp, vp], i32),
         "mps_barrier": ([P(ClockView), i32, vp], i32),
         "mps_reset_pad": ([P(ClockView), i32, vp], i32),
         "mps_straggle": ([C.c_longlong, vp], i32),

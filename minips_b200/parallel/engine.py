@@ -226,6 +226,9 @@ class Engine:
             self._done_work.wait()
 
     def _serve_until_done(self, task: MLTask):
+        """This rank owns shards of the task's tables but runs none of its workers.  For every BSP table a
+        resident device kernel (mps_fold_server) applies the clock edges as the workers' clocks arrive in
+        this rank's pad; the host only waits for the end of the task and then tells the kernels to stop."""
         import ctypes as C
         from ..ops import _lib
         if self.control.world == 1:
@@ -233,22 +236,18 @@ class Engine:
         done = self.dist.barrier(group=self.control.group, async_op=True)
         tabs = [self.tables[t] for t in task.get_tables()
                 if self.tables[t].model_type == ModelType.BSP and self.tables[t].own_count > 0]
-        clocks = {t.table_id: 0 for t in tabs}
-        while True:
-            finished = done.is_completed()
-            for t in tabs:
-                pad = t.pad_tensor()
-                mn = int(pad[_lib.PAD_PROGRESS:_lib.PAD_PROGRESS + t.num_workers].min().item())
-                while clocks[t.table_id] < mn:
-                    clocks[t.table_id] += 1
-                    cv = t.clock_view()
-                    _lib.check(t.lib.mps_clock(C.byref(t.view), C.byref(cv), -1, clocks[t.table_id], 1,
-                                               _lib.stream_ptr()), "clock(fold)")
-                torch.cuda.synchronize(self.device)
-            if finished:
-                break
-            time.sleep(0.0005)
+        flag = torch.zeros(1, dtype=torch.int32).pin_memory()
+        streams = []
+        for t in tabs:
+            s = torch.cuda.Stream(self.device)        # one resident kernel per table, side by side
+            start = int(t.pad_tensor()[_lib.PAD_FOLDED + t.own_first].item())
+            _lib.check(t.lib.mps_fold_server(C.byref(t.view), C.byref(t.clock_view()), start,
+                                             C.c_void_p(flag.data_ptr()), _lib.stream_ptr(s)), "fold_server")
+            streams.append(s)
         done.wait()
+        flag[0] = 1                                   # the kernels poll it through the pinned mapping
+        for s in streams:
+            s.synchronize()
 
     # ---- checkpoint hooks (engine.hpp:221-232) --------------------------------------------------
     def set_dump_callback(self, fn: Callable):

@@ -233,6 +233,34 @@ def main():
         assert took["ssp"] >= 8 * 3.0 - 1.0, (rank, took)      # may run at most staleness + 1 clocks ahead
         assert took["asp"] < took["ssp"] / 2, (rank, took)
 
+    # ---- 9. workers on rank 0 only: every other rank is a pure server of two BSP tables; their clock edges
+    #         are applied by the resident device fold kernel (no host poll)
+    t9a = engine.create_table(num_dims=50_000, model_type=ModelType.BSP)
+    t9b = engine.create_table(num_dims=7_001, model_type=ModelType.BSP, dtype=torch.float64)
+    seen9 = []
+
+    def solo_fn(info):
+        ta, tb = info.create_kv_client_table(t9a), info.create_kv_client_table(t9b)
+        ka, kb = torch.arange(0, 50_000, 3), torch.arange(7_001)
+        for it in range(6):
+            seen9.append((ta.get(ka).clone(), tb.get(kb).clone()))
+            ta.add(ka, torch.full((ka.numel(),), 2.0))
+            tb.add(kb, torch.full((kb.numel(),), 0.5, dtype=torch.float64))
+            ta.clock()
+            tb.clock()
+        seen9.append((ta.get(ka).clone(), tb.get(kb).clone()))
+
+    task9 = MLTask()
+    task9.set_worker_alloc([WorkerAlloc(engine.nodes[0].id, 1)])
+    task9.set_tables([t9a, t9b])
+    task9.set_lambda(solo_fn)
+    engine.run(task9)
+    if rank == 0:
+        for it, (a, b2) in enumerate(seen9):
+            assert torch.all(a == 2.0 * it) and torch.all(b2 == 0.5 * it), (it, a[:3].tolist(), b2[:3].tolist())
+    full9 = engine.tables[t9a].gather_full()
+    assert torch.all(full9[::3] == 12.0) and torch.all(full9[1::3] == 0.0), (rank, full9[:6].tolist())
+
     engine.stop_everything()
     import torch.distributed as dist
     if dist.is_initialized():
