@@ -107,7 +107,8 @@ def measure_lr(engine, args, data, dtype_name, want_e2e, want_timeline=False):
         tr = SparseLRTrainer(info.create_kv_client_table(tid), data, args.alpha)
         dense = tr.dense_regime(B)
         result["regime"] = "dense" if dense else "sparse"
-        result["protocol"] = ("xchg" if tr.xchg_ok() else "pushpull") if dense else "per-nnz"
+        result["protocol"] = (("xchg" if tr.xchg_ok() else "pushpull") if dense else
+                              ("bucket" if tr.bucket_ok() else "per-nnz"))
 
         def run(st_host):
             # dense regime: all iterations inside one persistent kernel; sparse regime (batch touches
@@ -134,7 +135,7 @@ def measure_lr(engine, args, data, dtype_name, want_e2e, want_timeline=False):
         result["times"] = times
         result["ms"] = statistics.median(times)
         result["loss_last"] = float(loss[-1, 0].item()) / B
-        result["launches"] = 1 if dense else 2 * K
+        result["launches"] = 1 if dense else (K if result["protocol"] == "bucket" else 2 * K)
         if dense and tr.xchg_ok():
             result["nvls"] = bool(engine.tables[tid].xchg.multicast)
             result["reduce"] = engine.tables[tid].xchg.reduce
@@ -240,8 +241,10 @@ def bench_lr_ours(args):
         "timed_region": (f"median of {len(result['times'])} regions of K steps, each bracketed by barrier + synchronize; "
                          "one persistent cooperative kernel runs the K iterations of a region (device-side clock gating)"
                          if result["regime"] == "dense" else
-                         f"median of {len(result['times'])} regions of K steps; per step one fused pull+SpMV+gradient+push "
-                         "kernel (per-nnz peer ld / red.add) + one clock kernel"),
+                         f"median of {len(result['times'])} regions of K steps; per step " +
+                         ("one kernel: keys / values / deltas travel as per-owner messages, Clock inside"
+                          if result["protocol"] == "bucket" else
+                          "one fused pull+SpMV+gradient+push kernel (per-nnz peer ld / red.add) + one clock kernel")),
         "repeats_ms": result["times"], "loss_last": result["loss_last"],
         "host_numa": engine.numa,
     }

@@ -192,7 +192,15 @@ lr_step_bucket_kernel(const __grid_constant__ MpsTableView v, const __grid_const
     const int o = (me + 1 + k) % R;
     const long long beg = s_off[o], cnt = s_off[o + 1] - beg;
     uint32_t* dst = bucket_ptrs<T>(b, o).inbox_keys + static_cast<int64_t>(me) * b.cap;
-    for (int64_t i = tid; i < cnt; i += nthreads) st_sys_u32(dst + i, send_keys[beg + i]);
+    // 16-byte peer stores (the inbox is aligned, the bucket inside send_keys need not be: 4 scalar loads)
+    const int64_t nq = cnt >> 2;
+    for (int64_t q = tid; q < nq; q += nthreads) {
+      const uint32_t* sp = send_keys + beg + 4 * q;
+      asm volatile("st.relaxed.sys.global.v4.b32 [%0], {%1,%2,%3,%4};" ::"l"(dst + 4 * q), "r"(sp[0]), "r"(sp[1]),
+                   "r"(sp[2]), "r"(sp[3])
+                   : "memory");
+    }
+    for (int64_t i = (nq << 2) + tid; i < cnt; i += nthreads) st_sys_u32(dst + i, send_keys[beg + i]);
     if (tid == 0) {
       int64_t* meta = bucket_ptrs<T>(b, o).inbox_meta + 2 * me;
       st_sys_s64(meta, cnt);
@@ -297,7 +305,16 @@ lr_step_bucket_kernel(const __grid_constant__ MpsTableView v, const __grid_const
     const int o = (me + 1 + k) % R;
     const long long beg = s_off[o], cnt = s_off[o + 1] - beg;
     T* dst = bucket_ptrs<T>(b, o).inbox_delta + static_cast<int64_t>(me) * b.cap;
-    for (int64_t i = tid; i < cnt; i += nthreads) st_sys(dst + i, delta_send[beg + i]);
+    constexpr int N = Chunk<T>::N;
+    const int64_t nq = cnt / N;
+    for (int64_t q = tid; q < nq; q += nthreads) {
+      const T* sp = delta_send + beg + N * q;
+      Chunk<T> ch;
+      if constexpr (N == 4) ch.v = make_float4(sp[0], sp[1], sp[2], sp[3]);
+      else ch.v = make_double2(sp[0], sp[1]);
+      st_sys_chunk(dst + N * q, ch);
+    }
+    for (int64_t i = nq * N + tid; i < cnt; i += nthreads) st_sys(dst + i, delta_send[beg + i]);
   }
   __syncthreads();
   if (threadIdx.x == 0) {

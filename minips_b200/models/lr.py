@@ -102,12 +102,15 @@ class XchgScratch:
         x.replica_mc = self.buf.mc_ptr or None
         x.gacc_mc = (self.buf.mc_ptr + self.stride_bytes) if self.buf.mc_ptr else None
         x.gacc_stride = self.stride_bytes // table.itemsize
-        # Measured on B200 / NVSwitch: fp64 has only a scalar multimem.ld_reduce, which loses to
-        # 16-byte peer loads on few GPUs; with two GPUs a plain peer store beats the multicast store.
+        # Measured on B200 / NVSwitch (tools/xchg_sweep.sh, profiles/round2/): fp32 is fastest through NVLS
+        # (multimem.ld_reduce.v4 / multimem.st.v4) from 4 GPUs up; fp64 has only a scalar
+        # multimem.ld_reduce and its 8-byte multicast stores drain slowly, so 16-byte peer loads / stores
+        # win at every size; with two GPUs a plain peer store beats the multicast store for fp32 too.
         how_r = os.environ.get("MINIPS_XCHG_REDUCE", "auto")
         how_b = os.environ.get("MINIPS_XCHG_BCAST", "auto")
-        p2p_r = how_r == "p2p" or (how_r == "auto" and table.dtype == torch.float64 and table.world < 4)
-        p2p_b = how_b == "p2p" or (how_b == "auto" and table.world <= 2)
+        f64 = table.dtype == torch.float64
+        p2p_r = how_r == "p2p" or (how_r == "auto" and f64)
+        p2p_b = how_b == "p2p" or (how_b == "auto" and (f64 or table.world <= 2))
         x.flags = (_lib.XCHG_REDUCE_P2P if p2p_r else 0) | (_lib.XCHG_BCAST_P2P if p2p_b else 0)
         self.c = x
         self.multicast = bool(self.buf.mc_ptr)

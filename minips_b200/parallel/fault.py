@@ -133,6 +133,11 @@ class FaultTolerantJob:
         none does within rollback_wait_s the failure is re-raised."""
         self.resume = getattr(self, "resume", False) or self.relaunched
         while True:
+            if self.resume:
+                # torch's symmetric-memory allocator keeps per-group state of the process group that died
+                # (a rendezvous on the new group waits for its time-out): generations after a rollback map
+                # their buffers through CUDA IPC, peer loads / stores instead of NVLS
+                os.environ["MINIPS_HEAP"] = "ipc"
             self._join()
             self.generations_run += 1
             failure: Optional[BaseException] = None

@@ -89,7 +89,8 @@ class SymmetricBuffer:
         worked before the collective rendezvous, so a rank that cannot allocate sends everybody to
         the IPC path instead of leaving the others inside a collective."""
         import os
-        if os.environ.get("MINIPS_HEAP", "symm") == "ipc":
+        # collective decision: one rank that wants plain IPC sends everybody there
+        if not all(self.control.all_gather(os.environ.get("MINIPS_HEAP", "symm") != "ipc")):
             return False
         dist = self.control.dist
         t, err = None, None

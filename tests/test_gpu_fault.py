@@ -96,3 +96,14 @@ def test_kill_a_rank_resume_equals_uninterrupted(tmp_path):
     assert wa.dtype == torch.float64 and wa.abs().max() > 0
     torch.testing.assert_close(wa, wb, rtol=1e-9, atol=1e-12)
     torch.testing.assert_close(torch.load(da / "w_2.pt"), wa, rtol=0, atol=0)   # every rank gathers the same table
+    # evidence for profiles/: the stamps of the run, in the order they were written
+    out_dir = os.path.join(ROOT, "gpurun_out")
+    if os.path.isdir(out_dir):
+        keep = ("[Fault Tolerance]", "checkpoint at iteration", "resumed from checkpoint", "generation",
+                "rollbacks ordered", "Total training time", "supervising")
+        with open(os.path.join(out_dir, "ft_gpu_kill_test.log"), "w") as f:
+            for name, text in (("master", mout), ("rank 0 (survivor)", outs[0]), ("rank 2 (relaunched)", relog)):
+                f.write(f"==== {name}\n")
+                f.writelines(l + "\n" for l in text.splitlines() if any(k in l for k in keep))
+            f.write(f"==== max |w_killed_and_recovered - w_uninterrupted| = {float((wa - wb).abs().max()):.3e} "
+                    f"(max |w| = {float(wa.abs().max()):.3e})\n")

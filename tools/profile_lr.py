@@ -15,7 +15,9 @@ ap = argparse.ArgumentParser()
 ap.add_argument("--ncu", action="store_true")
 ap.add_argument("--rows", type=int, default=2_000_000)
 ap.add_argument("--features", type=int, default=1_000_000)
+ap.add_argument("--dtype", default="fp64", choices=["fp64", "fp32"])
 a = ap.parse_args()
+DTYPE = torch.float64 if a.dtype == "fp64" else torch.float32
 
 node = Node(0, "localhost", 0)
 engine = Engine(node, [node], device=0)
@@ -26,7 +28,7 @@ PHASES = ["gate", "pull", "sync1", "rows+sync2", "pulled-wait", "push+signal"]
 
 
 def run(model, batch, iters, timeline=False):
-    tid = engine.create_table(num_dims=a.features, model_type=model, staleness=2)
+    tid = engine.create_table(num_dims=a.features, model_type=model, staleness=2, dtype=DTYPE)
     res = {}
 
     def fn(info):
