@@ -411,6 +411,24 @@ int mps_dense_lr_forward_tc(const MpsTableView* weights_view, const MpsClockView
                             const float* w_f32, const void* x_bf16, const float* label, int64_t n, int D,
                             float alpha, void* w16_scratch, float* w_f32_out, int* sync_ctr, float* coef,
                             float* loss_out, int max_ctas, void* stream);
+/* Forward AND gradient in one kernel that reads X once (csrc/kernels/dense_lr_fused.cu): 64-row tiles
+ * stay in shared memory between the logits product and the gradient product, which takes the same
+ * blocks as an MN-major A operand, so the whole kernel's gradient accumulates in TMEM and leaves it once:
+ * grad[d] += sum_r alpha (y_r - sigmoid(x_r . w)) x[r, d].  Same arguments as mps_dense_lr_forward_tc with
+ * `grad` [D] in place of `coef`; needs D % 8 == 0 and roundup(D, 128) <= 1024 (cudaErrorInvalidValue
+ * otherwise: use the two-kernel path). */
+int mps_dense_lr_step_tc(const MpsTableView* weights_view, const MpsClockView* clk, int progress,
+                         const float* w_f32, const void* x_bf16, const float* label, int64_t n, int D,
+                         float alpha, void* w16_scratch, float* w_f32_out, int* sync_ctr, float* grad,
+                         float* loss_out, int max_ctas, void* stream);
+/* The same one-pass iteration with the two matrix-vector products on the CUDA cores: TMA streams 64-row
+ * tiles into shared memory, weights and gradient accumulators live in registers for the whole kernel
+ * (csrc/kernels/dense_lr_stream.cu).  1 Mi x 1024 on one B200: 0.64 ms per iteration, the tcgen05
+ * variant above 0.66 ms, two passes 0.75 ms, PyTorch 0.73 ms.  Same limits on D. */
+int mps_dense_lr_step_stream(const MpsTableView* weights_view, const MpsClockView* clk, int progress,
+                             const float* w_f32, const void* x_bf16, const float* label, int64_t n, int D,
+                             float alpha, float* w_f32_out, float* grad, float* loss_out, int max_ctas,
+                             void* stream);
 /* Backward: grad[d] += sum_r coef[r] * x[r, d] (lr_example.cpp:305-312), feeds mps_push_dense. */
 int mps_dense_lr_grad(const void* x_bf16, const float* coef, int64_t n, int D, float* grad, void* stream);
 

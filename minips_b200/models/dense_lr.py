@@ -25,8 +25,14 @@ class DenseLRTrainer:
         self.D = x.shape[1]
         assert self.table.num_keys == self.D and self.table.dtype == torch.float32 and self.table.k == 1
         self.dev, self.lib = client.dev, client.lib
-        dp = (self.D + 63) // 64 * 64
+        dp = (self.D + 127) // 128 * 128
         self.w16 = torch.zeros(16 * dp, dtype=torch.bfloat16, device=self.dev)
+        # the one-pass kernels keep a 64-row tile of X in shared memory: D up to 1024.  "stream" (TMA ring +
+        # CUDA cores, 0.64 ms at 1 Mi x 1024) is the default; "mma" keeps both products on tcgen05, the second
+        # with the tile as an MN-major operand (0.66 ms); "twopass" = tcgen05 forward + gradient pass (0.75 ms)
+        import os
+        self.mode = os.environ.get("MINIPS_DENSE_LR", "stream") if dp <= 1024 else "twopass"
+        self.fused = self.mode in ("stream", "mma")
         self.w32 = torch.empty(self.D, dtype=torch.float32, device=self.dev)
         self.sync = torch.zeros(4, dtype=torch.int32, device=self.dev)
         self.grad = torch.zeros(self.D, dtype=torch.float32, device=self.dev)
@@ -59,7 +65,30 @@ class DenseLRTrainer:
         return self._coef, loss
 
     def step(self, start: int, batch: int, loss: Optional[torch.Tensor] = None) -> torch.Tensor:
-        """One iteration: Get (fused) -> forward -> gradient -> Add -> Clock."""
+        """One iteration: Get (fused) -> forward -> gradient -> Add -> Clock.  With D <= 1024 forward and
+        gradient are ONE tcgen05 kernel that reads X once (dense_lr_fused.cu)."""
+        if self.fused:
+            xb = self.x[start:start + batch]
+            if loss is None:
+                loss = torch.zeros(2, dtype=torch.float32, device=self.dev)
+            t, c = self.table, self.client
+            c._local_gate()
+            if self.mode == "stream":
+                _lib.check(self.lib.mps_dense_lr_step_stream(
+                    C.byref(t.view), C.byref(t.clock_view()), c.progress, None, C.c_void_p(xb.data_ptr()),
+                    C.c_void_p(self.label[start:start + batch].data_ptr()), xb.shape[0], self.D, self.alpha,
+                    C.c_void_p(self.w32.data_ptr()), C.c_void_p(self.grad.data_ptr()), C.c_void_p(loss.data_ptr()), 0,
+                    c._sp()), "dense_lr_step_stream")
+            else:
+                _lib.check(self.lib.mps_dense_lr_step_tc(
+                    C.byref(t.view), C.byref(t.clock_view()), c.progress, None, C.c_void_p(xb.data_ptr()),
+                    C.c_void_p(self.label[start:start + batch].data_ptr()), xb.shape[0], self.D, self.alpha,
+                    C.c_void_p(self.w16.data_ptr()), C.c_void_p(self.w32.data_ptr()),
+                    C.c_void_p(self.sync.data_ptr()), C.c_void_p(self.grad.data_ptr()), C.c_void_p(loss.data_ptr()),
+                    0, c._sp()), "dense_lr_step_tc")
+            self.client.add_all(self.grad, zero_src=True)
+            self.client.clock()
+            return loss
         coef, loss = self.forward(start, batch, loss)
         xb = self.x[start:start + batch]
         _lib.check(self.lib.mps_dense_lr_grad(C.c_void_p(xb.data_ptr()), C.c_void_p(coef.data_ptr()), xb.shape[0],

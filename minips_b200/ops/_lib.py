@@ -198,6 +198,10 @@ def _declare(lib):
                                   vp, i32, vp], i32),
         "mps_dense_lr_forward_tc": ([P(TableView), P(ClockView), i32, vp, vp, vp, i64, i32, f32, vp, vp, vp, vp, vp,
                                      i32, vp], i32),
+        "mps_dense_lr_step_tc": ([P(TableView), P(ClockView), i32, vp, vp, vp, i64, i32, f32, vp, vp, vp, vp, vp,
+                                  i32, vp], i32),
+        "mps_dense_lr_step_stream": ([P(TableView), P(ClockView), i32, vp, vp, vp, i64, i32, f32, vp, vp, vp, i32, vp],
+                                     i32),
         "mps_dense_lr_grad": ([vp, vp, i64, i32, vp, vp], i32),
         "mps_kmeans_tc_error": ([], i32),
         "mps_dense_lr_tc_error": ([], i32),

@@ -8,8 +8,13 @@ from minips_b200.parallel.types import MLTask, ModelType, Node, WorkerAlloc
 pytestmark = pytest.mark.gpu
 
 
+@pytest.mark.parametrize("mode", ["stream", "mma", "twopass"])
 @pytest.mark.parametrize("n,D", [(4096, 512), (10_007, 1000), (300, 64), (2048, 4096)])
-def test_dense_lr_training_matches_oracle(n, D):
+def test_dense_lr_training_matches_oracle(n, D, mode, monkeypatch):
+    """Three implementations of the iteration against the same oracle: "stream" (TMA-fed, X read once, the
+    default), "mma" (both products on tcgen05, the second one with the tile as an MN-major operand) and
+    "twopass" (tcgen05 forward + CUDA-core gradient pass; also what D > 1024 takes)."""
+    monkeypatch.setenv("MINIPS_DENSE_LR", mode)
     from minips_b200.models.dense_lr import DenseLRTrainer, oracle_step
     from minips_b200.parallel.engine import Engine
     node = Node(0, "localhost", 0)

@@ -59,6 +59,7 @@ def timed(fn, n):
 
 def worker(info):
     tr = DenseLRTrainer(info.create_kv_client_table(tid), x, y, alpha=1e-3 / B)
+    out["mode"] = tr.mode
     out["forward_ms"] = timed(lambda s: tr.forward(s, B), a.iters)
     out["step_ms"] = timed(lambda s: tr.step(s, B), a.iters)
     w = torch.zeros(a.D, device="cuda")
@@ -85,7 +86,9 @@ print(f"  forward (tcgen05, pull + sigmoid/loss fused): {out['forward_ms']:.3f} 
       f"{gb / out['forward_ms'] * 1e3:.0f} GB/s"
       f"  = {gb / out['forward_ms'] * 1e3 / HBM_GBS:.2f} of HBM copy peak   "
       f"[torch matmul+sigmoid: {out['torch_forward_ms']:.3f} ms]")
-print(f"  iteration (Get, forward, gradient, Add, Clock): {out['step_ms']:.3f} ms  "
-      f"{2 * gb / out['step_ms'] * 1e3:.0f} GB/s"
-      f"  = {2 * gb / out['step_ms'] * 1e3 / HBM_GBS:.2f} of HBM copy peak   {B / out['step_ms'] / 1e6:.2f} G samples/s"
+passes = 1 if out["mode"] in ("stream", "mma") else 2   # how often the iteration reads X from HBM
+print(f"  iteration [{out['mode']}: X read {passes}x] (Get, forward, gradient, Add, Clock): {out['step_ms']:.3f} ms  "
+      f"{passes * gb / out['step_ms'] * 1e3:.0f} GB/s of X traffic"
+      f"  = {passes * gb / out['step_ms'] * 1e3 / HBM_GBS:.2f} of HBM copy peak   "
+      f"{B / out['step_ms'] / 1e6:.2f} G samples/s"
       f"   [torch: {out['torch_step_ms']:.3f} ms, {B / out['torch_step_ms'] / 1e6:.2f} G samples/s]")
