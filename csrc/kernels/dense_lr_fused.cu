@@ -386,3 +386,6 @@ extern "C" int mps_dense_lr_step_tc(const MpsTableView* weights_view, const MpsC
                                         args, smem, st));
   return 0;
 }
+
+// this translation unit's mbarrier time-out flag (tc_common.cuh); mps_dense_lr_tc_error() collects them
+extern "C" int mps_dense_lr_fused_timeout(void) { return mps::tc::tc_take_timeout_flag(); }

@@ -278,3 +278,6 @@ extern "C" int mps_dense_lr_step_stream(const MpsTableView* weights_view, const 
   MPS_LAUNCH_CHECK();
   return 0;
 }
+
+// this translation unit's mbarrier time-out flag (tc_common.cuh); mps_dense_lr_tc_error() collects them
+extern "C" int mps_dense_lr_stream_timeout(void) { return mps::tc::tc_take_timeout_flag(); }

@@ -269,6 +269,14 @@ int mps_dense_lr_grad(const void* x_bf16, const float* coef, int64_t n, int D, f
 
 /* 1 if an mbarrier wait of a tcgen05 kernel of this file expired since the last call (clears the flag);
  * synchronises with the device. */
-int mps_dense_lr_tc_error(void) { return mps::tc::tc_take_timeout_flag(); }
+int mps_dense_lr_fused_timeout(void);
+int mps_dense_lr_stream_timeout(void);
+int mps_dense_lr_rows_timeout(void);
+// every dense-LR translation unit has its own copy of the flag
+int mps_dense_lr_tc_error(void) {
+  const int a = mps::tc::tc_take_timeout_flag(), b = mps_dense_lr_fused_timeout(), c = mps_dense_lr_stream_timeout(),
+            d = mps_dense_lr_rows_timeout();
+  return (a < 0 || b < 0 || c < 0 || d < 0) ? -1 : (a | b | c | d);
+}
 
 }  // extern "C"

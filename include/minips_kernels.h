@@ -430,6 +430,13 @@ int mps_dense_lr_step_stream(const MpsTableView* weights_view, const MpsClockVie
                              float alpha, float* w_f32_out, float* grad, float* loss_out, int max_ctas,
                              void* stream);
 /* Backward: grad[d] += sum_r coef[r] * x[r, d] (lr_example.cpp:305-312), feeds mps_push_dense. */
+/* The same iteration with NO tile resident: one warp owns one row from the load to the gradient, the
+ * shared-memory ring is filled by linear bulk copies and is only bytes in flight
+ * (csrc/kernels/dense_lr_rows.cu).  D % 8 == 0, D <= 1024, x 16-byte aligned. */
+int mps_dense_lr_step_rows(const MpsTableView* weights_view, const MpsClockView* clk, int progress,
+                           const float* w_f32, const void* x_bf16, const float* label, int64_t n, int D,
+                           float alpha, float* w_f32_out, float* grad, float* loss_out, int max_ctas,
+                           void* stream);
 int mps_dense_lr_grad(const void* x_bf16, const float* coef, int64_t n, int D, float* grad, void* stream);
 
 #ifdef __cplusplus

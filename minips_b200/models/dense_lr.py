@@ -32,7 +32,7 @@ class DenseLRTrainer:
         # with the tile as an MN-major operand (0.66 ms); "twopass" = tcgen05 forward + gradient pass (0.75 ms)
         import os
         self.mode = os.environ.get("MINIPS_DENSE_LR", "stream") if dp <= 1024 else "twopass"
-        self.fused = self.mode in ("stream", "mma")
+        self.fused = self.mode in ("rows", "stream", "mma")
         self.w32 = torch.empty(self.D, dtype=torch.float32, device=self.dev)
         self.sync = torch.zeros(4, dtype=torch.int32, device=self.dev)
         self.grad = torch.zeros(self.D, dtype=torch.float32, device=self.dev)
@@ -73,12 +73,13 @@ class DenseLRTrainer:
                 loss = torch.zeros(2, dtype=torch.float32, device=self.dev)
             t, c = self.table, self.client
             c._local_gate()
-            if self.mode == "stream":
-                _lib.check(self.lib.mps_dense_lr_step_stream(
+            if self.mode in ("rows", "stream"):
+                fn = self.lib.mps_dense_lr_step_rows if self.mode == "rows" else self.lib.mps_dense_lr_step_stream
+                _lib.check(fn(
                     C.byref(t.view), C.byref(t.clock_view()), c.progress, None, C.c_void_p(xb.data_ptr()),
                     C.c_void_p(self.label[start:start + batch].data_ptr()), xb.shape[0], self.D, self.alpha,
                     C.c_void_p(self.w32.data_ptr()), C.c_void_p(self.grad.data_ptr()), C.c_void_p(loss.data_ptr()), 0,
-                    c._sp()), "dense_lr_step_stream")
+                    c._sp()), "dense_lr_step_" + self.mode)
             else:
                 _lib.check(self.lib.mps_dense_lr_step_tc(
                     C.byref(t.view), C.byref(t.clock_view()), c.progress, None, C.c_void_p(xb.data_ptr()),

@@ -202,6 +202,8 @@ def _declare(lib):
                                   i32, vp], i32),
         "mps_dense_lr_step_stream": ([P(TableView), P(ClockView), i32, vp, vp, vp, i64, i32, f32, vp, vp, vp, i32, vp],
                                      i32),
+        "mps_dense_lr_step_rows": ([P(TableView), P(ClockView), i32, vp, vp, vp, i64, i32, f32, vp, vp, vp, i32, vp],
+                                   i32),
         "mps_dense_lr_grad": ([vp, vp, i64, i32, vp, vp], i32),
         "mps_kmeans_tc_error": ([], i32),
         "mps_dense_lr_tc_error": ([], i32),

@@ -8,7 +8,7 @@ from minips_b200.parallel.types import MLTask, ModelType, Node, WorkerAlloc
 pytestmark = pytest.mark.gpu
 
 
-@pytest.mark.parametrize("mode", ["stream", "mma", "twopass"])
+@pytest.mark.parametrize("mode", ["rows", "stream", "mma", "twopass"])
 @pytest.mark.parametrize("n,D", [(4096, 512), (10_007, 1000), (300, 64), (2048, 4096)])
 def test_dense_lr_training_matches_oracle(n, D, mode, monkeypatch):
     """Three implementations of the iteration against the same oracle: "stream" (TMA-fed, X read once, the

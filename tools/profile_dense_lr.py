@@ -86,7 +86,7 @@ print(f"  forward (tcgen05, pull + sigmoid/loss fused): {out['forward_ms']:.3f} 
       f"{gb / out['forward_ms'] * 1e3:.0f} GB/s"
       f"  = {gb / out['forward_ms'] * 1e3 / HBM_GBS:.2f} of HBM copy peak   "
       f"[torch matmul+sigmoid: {out['torch_forward_ms']:.3f} ms]")
-passes = 1 if out["mode"] in ("stream", "mma") else 2   # how often the iteration reads X from HBM
+passes = 1 if out["mode"] in ("rows", "stream", "mma") else 2   # how often the iteration reads X from HBM
 print(f"  iteration [{out['mode']}: X read {passes}x] (Get, forward, gradient, Add, Clock): {out['step_ms']:.3f} ms  "
       f"{passes * gb / out['step_ms'] * 1e3:.0f} GB/s of X traffic"
       f"  = {passes * gb / out['step_ms'] * 1e3 / HBM_GBS:.2f} of HBM copy peak   "
