@@ -16,6 +16,9 @@
 //   warp 0      producer: cp.async.bulk global -> shared, completion on the stage's mbarrier;
 //   warps 1-15  consumers: 2 rows per warp and stage (16 warps in all, so every thread has 128 registers
 //               for its 32 weights, 32 accumulators and the row in flight).
+// Measured at 1 Mi x 1024 bf16 on one B200 (tools/dense_lr_modes.sh, whole iteration incl. Get / Add /
+// Clock): 0.349 ms = 6.15 TB/s = 0.94 of the measured HBM copy rate (stream 0.64 ms, tcgen05 0.66 ms, PyTorch
+// 0.72 ms).  About 180 instructions per row and lane, half of the issue slots at that rate.
 // At the end the 15 warps' accumulators meet in shared memory (the ring is free by then) and leave with one
 // red.add per feature and CTA.
 // Reference op: apps/logistic_regression/lr_example.cpp:293-312 for dense rows.
@@ -58,6 +61,12 @@ __device__ __forceinline__ void bulk_load(void* dst, const void* src, uint32_t b
                    smem_u32(dst)),
                "l"(src), "r"(bytes), "r"(smem_u32(bar))
                : "memory");
+}
+
+__device__ __forceinline__ uint4 lds128(uint32_t addr) {
+  uint4 v;
+  asm volatile("ld.shared.v4.u32 {%0, %1, %2, %3}, [%4];" : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "r"(addr) : "memory");
+  return v;
 }
 
 __global__ void __launch_bounds__(kThreads, 1) dense_lr_rows_kernel(const __grid_constant__ Params p) {
@@ -134,25 +143,33 @@ __global__ void __launch_bounds__(kThreads, 1) dense_lr_rows_kernel(const __grid
   };
   fetch_labels(0);
 
+  // everything that does not change per row is computed once: which of my 4 chunks exist, and the byte
+  // offset of my first row's first chunk inside a stage (32-bit shared address arithmetic from here on)
+  bool on[4];
+#pragma unroll
+  for (int c = 0; c < 4; ++c) on[c] = lane + 32 * c < nch;
+  const uint32_t sx = smem_u32(sX);
+  const uint32_t my_off = static_cast<uint32_t>(cw * kRPW) * row_bytes + static_cast<uint32_t>(lane) * 16;
+  const float alpha = p.alpha;
+
   uint32_t s = 0, ph = 0;
   for (int64_t i = 0; i < my_tiles; ++i) {
-    const int64_t row0 = (blockIdx.x + i * gridDim.x) * kTileRows;
+    const int64_t left = p.n - (blockIdx.x + i * gridDim.x) * kTileRows;
+    const int rows_here = left < kTileRows ? static_cast<int>(left) : kTileRows;
     float y[kRPW];
 #pragma unroll
     for (int rr = 0; rr < kRPW; ++rr) y[rr] = y_next[rr];
     fetch_labels(i + 1);
     mbar_wait(full + s, ph);
-    const uint8_t* tile = sX + static_cast<size_t>(s) * p.stage_bytes;
+    uint32_t addr = sx + s * p.stage_bytes + my_off;
 #pragma unroll 1
-    for (int rr = 0; rr < kRPW; ++rr) {
-      const int r = cw * kRPW + rr;
-      const bool live = row0 + r < p.n;  // warp-uniform
+    for (int rr = 0; rr < kRPW; ++rr, addr += row_bytes) {
+      const bool live = cw * kRPW + rr < rows_here;  // warp-uniform; false only in the last tile of the batch
       uint4 x[4];
 #pragma unroll
       for (int c = 0; c < 4; ++c) {
         x[c] = make_uint4(0u, 0u, 0u, 0u);
-        if (live && lane + 32 * c < nch)
-          x[c] = *reinterpret_cast<const uint4*>(tile + static_cast<uint32_t>(r) * row_bytes + (lane + 32 * c) * 16);
+        if (on[c] && live) x[c] = lds128(addr + 512 * c);
       }
       float acc[4] = {0.f, 0.f, 0.f, 0.f};  // one chain per chunk
 #pragma unroll
@@ -169,11 +186,15 @@ __global__ void __launch_bounds__(kThreads, 1) dense_lr_rows_kernel(const __grid
       }
       const float z = warp_sum((acc[0] + acc[1]) + (acc[2] + acc[3]));
       const float yr = rr == 0 ? y[0] : y[kRPW - 1];
+      // one exponential serves the sigmoid and the loss: e = exp(-|z|), sigmoid = (z >= 0 ? 1 : e) / (1 + e),
+      // logloss = max(z, 0) - y z + log(1 + e)
+      const float e = __expf(-fabsf(z));
+      const float inv = __fdividef(1.f, 1.f + e);
+      const float pred = z >= 0.f ? inv : e * inv;
       float coef = 0.f;
       if (live) {
-        const float pred = 1.f / (1.f + __expf(-z));
-        coef = p.alpha * (yr - pred);
-        loss += fmaxf(z, 0.f) + log1pf(__expf(-fabsf(z))) - yr * z;
+        coef = alpha * (yr - pred);
+        loss += fmaxf(z, 0.f) - yr * z + __logf(1.f + e);
         correct += ((pred > 0.5f) == (yr > 0.5f)) ? 1.f : 0.f;
       }
 #pragma unroll

@@ -10,6 +10,8 @@
 // one 0.66 ms, two passes 0.75 ms, PyTorch (two cuBLAS GEMVs) 0.73 ms.  Both one-pass kernels are held
 // back by residency, not by HBM (0.33 ms at the copy rate): a 64-row tile must stay in shared memory from
 // its first block until its gradient is done, and 227 KiB hold one tile plus 6-10 blocks of the next.
+// dense_lr_rows.cu removes the residency (one warp owns a row end to end) and runs at 0.35 ms; it is the
+// default, this kernel and the tcgen05 one stay selectable (MINIPS_DENSE_LR).
 //   warp 0      TMA producer: 64-row x 64-column blocks of X (bf16, 128B swizzle) into a ring that holds
 //               one tile plus the first blocks of the next;
 //   warps 1-16  per tile: forward  - one warp per row, every lane owns 32 features whose weights stay in

@@ -432,7 +432,8 @@ int mps_dense_lr_step_stream(const MpsTableView* weights_view, const MpsClockVie
 /* Backward: grad[d] += sum_r coef[r] * x[r, d] (lr_example.cpp:305-312), feeds mps_push_dense. */
 /* The same iteration with NO tile resident: one warp owns one row from the load to the gradient, the
  * shared-memory ring is filled by linear bulk copies and is only bytes in flight
- * (csrc/kernels/dense_lr_rows.cu).  D % 8 == 0, D <= 1024, x 16-byte aligned. */
+ * (csrc/kernels/dense_lr_rows.cu).  1 Mi x 1024 on one B200: 0.349 ms per iteration = 0.94 of the HBM copy
+ * rate.  D % 8 == 0, D <= 1024, x 16-byte aligned. */
 int mps_dense_lr_step_rows(const MpsTableView* weights_view, const MpsClockView* clk, int progress,
                            const float* w_f32, const void* x_bf16, const float* label, int64_t n, int D,
                            float alpha, float* w_f32_out, float* grad, float* loss_out, int max_ctas,

@@ -27,11 +27,13 @@ class DenseLRTrainer:
         self.dev, self.lib = client.dev, client.lib
         dp = (self.D + 127) // 128 * 128
         self.w16 = torch.zeros(16 * dp, dtype=torch.bfloat16, device=self.dev)
-        # the one-pass kernels keep a 64-row tile of X in shared memory: D up to 1024.  "stream" (TMA ring +
-        # CUDA cores, 0.64 ms at 1 Mi x 1024) is the default; "mma" keeps both products on tcgen05, the second
-        # with the tile as an MN-major operand (0.66 ms); "twopass" = tcgen05 forward + gradient pass (0.75 ms)
+        # one-pass kernels (X crosses HBM once), D up to 1024, whole iteration at 1 Mi x 1024 on one B200:
+        # "rows" (default; one warp per row, bulk-copy ring, nothing resident) 0.349 ms = 0.94 of the HBM copy
+        # rate; "stream" (TMA ring + CUDA cores, 64-row tile resident) 0.64 ms; "mma" (both products on tcgen05,
+        # the second with the tile as an MN-major operand) 0.66 ms; "twopass" = tcgen05 forward + gradient pass
+        # 0.75 ms; PyTorch (two cuBLAS GEMVs) 0.72 ms
         import os
-        self.mode = os.environ.get("MINIPS_DENSE_LR", "stream") if dp <= 1024 else "twopass"
+        self.mode = os.environ.get("MINIPS_DENSE_LR", "rows") if dp <= 1024 else "twopass"
         self.fused = self.mode in ("rows", "stream", "mma")
         self.w32 = torch.empty(self.D, dtype=torch.float32, device=self.dev)
         self.sync = torch.zeros(4, dtype=torch.int32, device=self.dev)
@@ -66,7 +68,7 @@ class DenseLRTrainer:
 
     def step(self, start: int, batch: int, loss: Optional[torch.Tensor] = None) -> torch.Tensor:
         """One iteration: Get (fused) -> forward -> gradient -> Add -> Clock.  With D <= 1024 forward and
-        gradient are ONE tcgen05 kernel that reads X once (dense_lr_fused.cu)."""
+        gradient are ONE kernel that reads X once (dense_lr_rows.cu by default; MINIPS_DENSE_LR picks another)."""
         if self.fused:
             xb = self.x[start:start + batch]
             if loss is None:
