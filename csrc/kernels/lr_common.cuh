@@ -104,9 +104,13 @@ __device__ __forceinline__ void mc_st_chunk(float* p, const Chunk<float>& c) {
                "f"(c.v.z), "f"(c.v.w)
                : "memory");
 }
+// a store does not interpret its payload: the two doubles travel as ONE 16-byte packet (multimem.st has no
+// v2.f64 form; two scalar f64 stores make twice the packets and drain slowly)
 __device__ __forceinline__ void mc_st_chunk(double* p, const Chunk<double>& c) {
-  asm volatile("multimem.st.relaxed.sys.global.f64 [%0], %1;" ::"l"(p), "d"(c.v.x) : "memory");
-  asm volatile("multimem.st.relaxed.sys.global.f64 [%0], %1;" ::"l"(p + 1), "d"(c.v.y) : "memory");
+  asm volatile("multimem.st.relaxed.sys.global.v4.f32 [%0], {%1,%2,%3,%4};" ::"l"(p),
+               "f"(__int_as_float(__double2loint(c.v.x))), "f"(__int_as_float(__double2hiint(c.v.x))),
+               "f"(__int_as_float(__double2loint(c.v.y))), "f"(__int_as_float(__double2hiint(c.v.y)))
+               : "memory");
 }
 __device__ __forceinline__ void mc_st(float* p, float x) {
   asm volatile("multimem.st.relaxed.sys.global.f32 [%0], %1;" ::"l"(p), "f"(x) : "memory");
