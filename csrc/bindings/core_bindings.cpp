@@ -157,6 +157,9 @@ PYBIND11_MODULE(_minips_core, m) {
   m.def("dump_config_data", [](const std::map<int, int>& m2,
       const std::string& p) { lib::SVMDumper::DumpConfigData(m2, p); },
         py::arg("iter_map"), py::arg("path") = "");
+  m.def("dump_scale_file", [](const Node& n, const std::string& p) { lib::SVMDumper::DumpScaleFile(n, p); },
+        py::arg("node"), py::arg("path"));
+  m.def("load_scale_file", [](const std::string& p) { return lib::SVMDumper::LoadScaleFile(p); }, py::arg("path"));
 
   // ---- engine
   py::class_<Table>(m, "KVClientTable")
@@ -231,6 +234,14 @@ PYBIND11_MODULE(_minips_core, m) {
                (*shared)(failed);
              });
            })
+      .def("set_scale_hook",
+           [](Master& m2, py::function fn) {
+             auto shared = std::make_shared<py::function>(std::move(fn));
+             m2.SetScaleHook([shared](uint32_t node_id) {
+               py::gil_scoped_acquire gil;
+               (*shared)(node_id);
+             });
+           })
       .def("recovering_node", [](Master& m2) { return m2.GetMasterThread()->GetRecoveringNodeId(); })
       .def("all_quit", [](Master& m2) { return m2.GetMasterThread()->AllQuit(); })
       .def("heartbeats", [](Master& m2) {
@@ -245,5 +256,6 @@ PYBIND11_MODULE(_minips_core, m) {
       .def("stop", &ControlAgent::Stop, py::arg("quit_heartbeat") = true, py::call_guard<py::gil_scoped_release>())
       .def("need_rollback", &ControlAgent::NeedRollBack)
       .def("clear_rollback", &ControlAgent::ClearRollBack)
-      .def("rollback_count", &ControlAgent::RollBackCount);
+      .def("rollback_count", &ControlAgent::RollBackCount)
+      .def("scale", &ControlAgent::Scale);
 }

@@ -3,6 +3,8 @@
 #include <chrono>
 #include <cstdlib>
 
+#include "core/lib.hpp"
+
 namespace minips {
 
 // ------------------------------------------------------------------ MasterThread
@@ -13,6 +15,12 @@ void MasterThread::Init(const std::vector<Node>& nodes) {
   for (const auto& n : nodes) heartbeats_[n.id] = now;
   serving_nodes_ = nodes.size();
   quit_count_ = 0;
+}
+
+void MasterThread::AddNode(uint32_t id) {
+  std::lock_guard<std::mutex> lk(mu_);
+  if (heartbeats_.find(id) == heartbeats_.end()) ++serving_nodes_;
+  heartbeats_[id] = std::time(nullptr);
 }
 
 std::map<uint32_t, time_t> MasterThread::GetHeartBeats() {
@@ -165,7 +173,29 @@ void Master::RollBack(uint32_t failed_node_id) {
   engine_->RollBack(failed_node_id);
 }
 
-void Master::ScaleRollBack(uint32_t scale_node_id) { engine_->ScaleRollBack(scale_node_id); }
+void Master::ScaleRollBack(uint32_t scale_node_id) {
+  // the new node announced its address in the scale file (lib/svm_dumper.hpp:95-126); the master joins
+  // it to its node list so that kScaleRollback reaches it too and its heartbeats / goodbye are counted
+  // (the reference's peers Connect() to it the same way, comm/mailbox.cpp:197-219)
+  bool known = false;
+  for (const auto& n : nodes_) known = known || n.id == scale_node_id;
+  if (!known) {
+    const std::string path = Context::get_instance().get_string("scale_file");
+    if (!path.empty()) {
+      const Node n = lib::SVMDumper::LoadScaleFile(path);
+      if (n.id == scale_node_id) {
+        nodes_.push_back(n);
+        engine_->UpdateNodes(nodes_);
+        engine_->GetMailbox()->ConnectTo(n);
+        master_thread_->AddNode(n.id);
+      } else {
+        MINIPS_LOG(0) << "scale file " << path << " names node " << n.id << ", kScale came from " << scale_node_id;
+      }
+    }
+  }
+  if (scale_hook_) scale_hook_(scale_node_id);
+  engine_->ScaleRollBack(scale_node_id);
+}
 
 // ------------------------------------------------------------------ ControlAgent
 ControlAgent::ControlAgent(const Node& node, const std::vector<Node>& nodes, const Node& master_node)
@@ -190,6 +220,10 @@ void ControlAgent::Start() {
   engine_->GetMailbox()->ConnectAll();
   engine_->StartHeartbeatThread();
   started_ = true;
+}
+
+void ControlAgent::Scale() {
+  if (engine_) engine_->Scale(node_.id);
 }
 
 void ControlAgent::Stop(bool quit_heartbeat) {

@@ -30,6 +30,8 @@ class MasterThread : public Actor {
   MasterThread(uint32_t id, Master* master) : Actor(id), master_(master) {}
   void Init(const std::vector<Node>& nodes);
   std::map<uint32_t, time_t> GetHeartBeats();
+  // a node joined the cluster (scale-out): its heartbeats are tracked and its kQuitHeartBeat is awaited
+  void AddNode(uint32_t id);
   void SetRecoveringNodeId(int id) { recovering_node_id_ = id; }
   int GetRecoveringNodeId() const { return recovering_node_id_; }
   bool AllQuit() const { return all_quit_; }
@@ -83,6 +85,9 @@ class ControlAgent {
   bool NeedRollBack() const { return engine_ && engine_->IsNeedRollBack(); }
   void ClearRollBack() { if (engine_) engine_->SetNeedRollBack(false); }
   int RollBackCount() const { return engine_ ? engine_->GetRollBackSignals() : 0; }
+  // announce this node to the master as a scale-out node (driver/engine.hpp:81-90; the node first wrote
+  // its id:host:port into the scale file, lr_example.cpp:396-409)
+  void Scale();
   Engine* GetEngine() { return engine_.get(); }
 
  private:
@@ -99,6 +104,9 @@ class Master {
   // called on the master thread right before kRollBack is broadcast (the device backend bumps the
   // rendezvous generation here so that every rank that receives the message finds the new one)
   void SetRollBackHook(std::function<void(uint32_t)> f) { rollback_hook_ = std::move(f); }
+  // called on the master thread when a node announced itself with kScale, after the node was added to the
+  // master's node list and before kScaleRollback is broadcast
+  void SetScaleHook(std::function<void(uint32_t)> f) { scale_hook_ = std::move(f); }
   void StartMaster();                 // bring-up: id mapper + mailbox + sender + the two actors
   void StopMaster();                  // blocks until every node quit (or Shutdown was called)
   void Shutdown();                    // tear down without waiting for the nodes
@@ -114,6 +122,7 @@ class Master {
   std::unique_ptr<MasterThread> master_thread_;
   std::unique_ptr<HeartBeatCheckThread> heartbeat_check_;
   std::function<void(uint32_t)> rollback_hook_;
+  std::function<void(uint32_t)> scale_hook_;
   bool started_ = false;
 };
 

@@ -51,6 +51,14 @@ def _train(engine, ctx, job=None):
         data = make_synthetic(ctx.get_int32("num_samples"), num_dims, ctx.get_int32("nnz_per_row"), dev,
                               seed=ctx.get_int32("seed") + rank)
 
+    if not ctx.get_bool("keep_empty_nodes"):
+        # lr_example.cpp:145-152: a node that read no data leaves the cluster before the tables exist; the
+        # others go on without it (its GPU holds no shard)
+        if not engine.force_quit(data.n_rows == 0):
+            print(f"[node {engine.node.id}] ForceQuit the engine as no data allocated", flush=True)
+            engine.stop_everything()
+            return
+        rank, world = engine.rank_index, len(engine.nodes)
     model = ModelType[ctx.get_string("kModelType")]
     storage = StorageType[ctx.get_string("kStorageType")]
     dtype = torch.float64 if ctx.get_string("dtype") == "fp64" else torch.float32
@@ -73,9 +81,8 @@ def _train(engine, ctx, job=None):
     p_straggle = ctx.get_double("with_injected_straggler")
     pause_at, pause_s = ctx.get_int32("pause_at_iter"), ctx.get_double("pause_s")
     workers_per_node = max(1, ctx.get_int32("num_workers_per_node"))
-    # a node without local samples still takes part in every collective of the run (table, restore,
-    # barriers, checkpoints) but runs no worker: peers would hang in them if it just left
-    # (the reference sends kForceQuit instead, lr_example.cpp:145-152)
+    # --keep_empty_nodes: a node without local samples stays as a server-only rank (its HBM keeps its share of
+    # the table); it takes part in every collective of the run but runs no worker
     has_data = [bool(x) for x in engine.control.all_gather(data.n_rows > 0)]
     if not has_data[rank]:
         print(f"[node {engine.node.id}] no local data: serving its shards only", flush=True)
@@ -158,6 +165,7 @@ def main(argv=None):
     ctx.define("store_port", 29700, "rendezvous store of the fault-tolerant mode (hosted by the master)")
     ctx.define("relaunched", False, "set by the master's relaunch hook: wait for its rollback order before joining")
     ctx.define("weights_out", "", "write the final table to <prefix>_<node id>.pt")
+    ctx.define("keep_empty_nodes", False, "a node without data serves its shards instead of leaving (ForceQuit)")
     ctx.define("pause_at_iter", 0, "fault-injection aid: hold the first generation at this iteration")
     ctx.define("pause_s", 0.0, "... for this many seconds")
     ctx.parse(argv)
@@ -169,13 +177,23 @@ def main(argv=None):
         from ..parallel.fault import FaultTolerantJob
         os.environ.setdefault("MINIPS_SPIN_TIMEOUT_S", "5")
         core.context_set("checkpoint_file_prefix", ctx.get_string("checkpoint_file_prefix"))
+        scale_node = None
+        if ctx.get_bool("scale"):
+            # elastic scale-out (lr_example.cpp:396-409): this process is a NEW node joining a running job
+            scale_node = core.Node(ctx.get_int32("my_id"), ctx.get_string("scale_name") or "localhost",
+                                   ctx.get_int32("scale_port"))
+            print(f"[node {scale_node.id}] scaling out: joining as {scale_node.hostname}:{scale_node.port}", flush=True)
         job = FaultTolerantJob(core.parse_file(ctx.get_string("config_file")), ctx.get_int32("my_id"), hb,
-                               ctx.get_int32("store_port"), relaunched=ctx.get_bool("relaunched"))
-        device = int(os.environ.get("LOCAL_RANK", job.rank))
-        torch.cuda.set_device(device)
+                               ctx.get_int32("store_port"), relaunched=ctx.get_bool("relaunched"),
+                               scale_node=scale_node, scale_file=ctx.get_string("scale_file"))
         job.start()
+        gpu = {}
 
         def body(job):
+            if "device" not in gpu:       # a process keeps its GPU across generations
+                gpu["device"] = int(os.environ.get("LOCAL_RANK", job.rank))
+                torch.cuda.set_device(gpu["device"])
+            device = gpu["device"]
             nodes = [Node(n.id, n.hostname, n.port) for n in job.rank_nodes]
             engine = Engine(nodes[job.rank], nodes, device=device)
             try:

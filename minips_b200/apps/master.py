@@ -23,13 +23,14 @@ def main(argv=None):
     ctx.define("heartbeat_interval", "1", "seconds")
     ctx.define("relaunch_cmd", "", "command that restarts a node; the failed node id is appended")
     ctx.define("store_port", "29700", "TCP port of the rendezvous store (master host)")
+    ctx.define("scale_file", "", "where a scale-out node writes its id:host:port (shared path)")
     ctx.parse(argv)
     nodes = core.parse_file(ctx.get_string("config_file"))
     mp = MasterProcess(nodes, ctx.get_int32("heartbeat_interval"), ctx.get_string("relaunch_cmd"),
-                       ctx.get_int32("store_port"))
+                       ctx.get_int32("store_port"), ctx.get_string("scale_file"))
     print(f"[master] node {mp.master_node.id} supervising {[n.id for n in mp.rank_nodes]}", flush=True)
     mp.serve()
-    print(f"[master] every node quit; rollbacks ordered for {mp.rollbacks}", flush=True)
+    print(f"[master] every node quit; rollbacks ordered for {mp.rollbacks}, scale-outs for {mp.scaled}", flush=True)
     return 0
 
 

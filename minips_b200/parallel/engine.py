@@ -68,6 +68,7 @@ class Engine:
         self.dump_callback: Optional[Callable] = None
         self.context: Dict[str, object] = {}
         self.iteration_map: Dict[int, int] = {}
+        self.default_iteration = 0      # where a worker that is in no checkpoint starts (set by a re-sharding restore)
         self.started = False
         self.numa = None
         self.rank_index = 0
@@ -98,6 +99,42 @@ class Engine:
 
     StartEverything = start_everything
     StopEverything = stop_everything
+
+    def force_quit(self, leaving: bool) -> bool:
+        """Elastic shrink: nodes with `leaving` set leave the cluster before training (the reference's
+        data-less node broadcasts kForceQuit, lr_example.cpp:145-152; its peers drop it from the node list,
+        the barrier accounting and the id mapper: comm/mailbox.cpp:159-171, driver/engine.cpp:33-36).
+
+        Collective over the current nodes, called after start_everything and BEFORE any table exists.  The
+        survivors get a control group, node list and id mapper over the remaining nodes, so every table
+        created afterwards is partitioned over the survivors' HBM only.  Returns False on a leaving node:
+        it calls stop_everything and returns, like the reference."""
+        assert self.started and not self.tables, "membership changes before the tables are created"
+        flags = [bool(x) for x in self.control.all_gather(bool(leaving))]
+        if not any(flags):
+            return True
+        keep = [i for i, f in enumerate(flags) if not f]
+        assert keep, "every node asked to leave"
+        self.left_nodes = [self.nodes[i] for i, f in enumerate(flags) if f]
+        if flags[self.rank]:
+            self.started = False
+            return False
+        dist = self.dist
+        sub = self._group
+        if self.control.world > 1:
+            ranks = [dist.get_global_rank(self._group, i) if self._group is not None else i for i in keep]
+            # only the survivors create the group (the others are on their way out)
+            sub = dist.new_group(ranks=ranks, backend="gloo", use_local_synchronization=True)
+        self.nodes = [self.nodes[i] for i in keep]
+        self._group = sub
+        self.control = _ControlPlane(sub)
+        self.rank = self.control.rank
+        self.rank_index = self.rank
+        self.id_mapper = SimpleIdMapper(self.node, self.nodes)
+        self.id_mapper.init(self.num_server_threads_per_node)
+        return True
+
+    ForceQuit = force_quit
 
     # ---- tables (engine.hpp:289-357) ------------------------------------------------------------
     def get_ranges(self, num_dims: int) -> List[Range]:
@@ -283,7 +320,7 @@ class Engine:
         self.iteration_map[worker_id] = iteration
 
     def get_iteration(self, worker_id: int) -> int:
-        return self.iteration_map.get(worker_id, 0)
+        return self.iteration_map.get(worker_id, self.default_iteration)
 
     # ---- convenience ----------------------------------------------------------------------------
     @classmethod

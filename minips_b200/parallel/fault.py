@@ -17,6 +17,17 @@ bumps `generation` right before it broadcasts kRollBack, so whoever receives the
 
     master:   python -m minips_b200.apps.master --config_file=... --heartbeat_interval=1 --relaunch_cmd=...
     ranks:    python -m minips_b200.apps.lr_example --config_file=... --my_id=N --heartbeat_interval=1 ...
+
+Elastic scale-out (reference: lr_example.cpp:396-409, driver/engine.hpp:81-114, master/master_thread.cpp:
+40-43, comm/mailbox.cpp:197-219) is the same mechanism with a changed membership: a NEW process started
+with --scale --my_id=K --scale_name=host --scale_port=P writes its address into the scale file, starts
+its control agent and sends kScale; the master adds it to its node list, publishes the membership of the
+next generation, bumps `generation` and broadcasts kScaleRollback.  Every rank — old and new — meets in
+that generation with world + 1, the tables are partitioned over all of them (the new GPU's HBM takes its
+share: the restore re-shards, utils/checkpoint.py) and training resumes at the checkpointed iteration.
+
+    new rank: python -m minips_b200.apps.lr_example --config_file=... --scale --my_id=K --scale_name=host \
+                  --scale_port=P --scale_file=/shared/scale --heartbeat_interval=1 ...
 """
 from __future__ import annotations
 
@@ -44,15 +55,22 @@ class FaultTolerantJob:
     ordered a rollback."""
 
     def __init__(self, nodes, my_id: int, heartbeat_interval: int, store_port: int, relaunched: bool = False,
-                 pg_timeout_s: float = 60.0, rollback_wait_s: Optional[float] = None, backend: str = "gloo"):
+                 pg_timeout_s: float = 60.0, rollback_wait_s: Optional[float] = None, backend: str = "gloo",
+                 scale_node=None, scale_file: str = ""):
         from .. import core
         self.core = core
         self.master, self.rank_nodes = split_master(nodes, heartbeat_interval)
         assert self.master.is_master, "fault tolerance needs heartbeat_interval > 0 and a node with id 1"
+        self.scale_node = scale_node          # this process joins a running job as a new node
+        self.scale_file = scale_file
+        if scale_node is not None:
+            assert scale_node.id == my_id and my_id not in [n.id for n in nodes], "a scale node needs a fresh id"
+            self.rank_nodes = list(self.rank_nodes) + [scale_node]
+        self.known = {n.id: n for n in self.rank_nodes}
         ids = [n.id for n in self.rank_nodes]
         assert my_id in ids, f"node {my_id} is not a worker node of this cluster"
         self.my_id = my_id
-        self.rank = ids.index(my_id)
+        self.rank = ids.index(my_id)          # both are re-read from the store at every generation
         self.world = len(ids)
         self.me = self.rank_nodes[self.rank]
         self.interval = int(heartbeat_interval)
@@ -79,7 +97,21 @@ class FaultTolerantJob:
         host = "127.0.0.1" if self.master.hostname == "localhost" else self.master.hostname
         self.store = dist.TCPStore(host, self.store_port, is_master=False, timeout=timedelta(seconds=120),
                                    wait_for_workers=False)
-        if self.relaunched:
+        if self.scale_node is not None:
+            # lr_example.cpp:396-409: announce the address (scale file + store), then kScale; the master's
+            # answer is kScaleRollback and a new generation whose membership includes this node
+            before = int(self.store.add("generation", 0))
+            self.store.set(f"node/{self.my_id}", f"{self.me.hostname}:{self.me.port}")
+            if self.scale_file:
+                core.dump_scale_file(self.me, self.scale_file)
+            self.agent.scale()
+            end = time.time() + self.rollback_wait_s
+            while time.time() < end and int(self.store.add("generation", 0)) == before:
+                time.sleep(0.05)
+            assert int(self.store.add("generation", 0)) > before, "the master did not answer kScale"
+            self._await_rollback(5.0)         # the kScaleRollback addressed to this node: consumed here
+            self.resume = True
+        elif self.relaunched:
             # my first heartbeat makes the master order the rollback; the generation to join is the one it
             # publishes with that order
             self._await_rollback(self.rollback_wait_s)
@@ -91,7 +123,9 @@ class FaultTolerantJob:
 
     def check(self):
         if self.agent is not None and self.agent.need_rollback():
-            raise RollbackSignal()
+            if int(self.store.add("generation", 0)) > self.generation:
+                raise RollbackSignal()
+            self.agent.clear_rollback()       # an order for the generation this process already runs in
 
     def sleep(self, seconds: float):
         """Host-side wait that stays responsive to a rollback order."""
@@ -110,9 +144,25 @@ class FaultTolerantJob:
         return False
 
     # ---- generations --------------------------------------------------------------------------------
+    def _members(self, generation: int):
+        """Node ids of a generation, in rank order (published by the master before it bumps `generation`)."""
+        from .. import core
+        key = f"members/{generation}"
+        self.store.wait([key])
+        ids = [int(x) for x in self.store.get(key).decode().split(",") if x]
+        for i in ids:
+            if i not in self.known:           # a node that scaled in after this process started
+                host, port = self.store.get(f"node/{i}").decode().rsplit(":", 1)
+                self.known[i] = core.Node(i, host, int(port))
+        return ids
+
     def _join(self):
         import torch.distributed as dist
         self.generation = int(self.store.add("generation", 0))
+        ids = self._members(self.generation)
+        assert self.my_id in ids, f"node {self.my_id} is not a member of generation {self.generation}: {ids}"
+        self.rank_nodes = [self.known[i] for i in ids]
+        self.rank, self.world = ids.index(self.my_id), len(ids)
         prefix = dist.PrefixStore(f"gen{self.generation}/", self.store)
         dist.init_process_group(self.backend, store=prefix, rank=self.rank, world_size=self.world,
                                 timeout=timedelta(seconds=self.pg_timeout_s))
@@ -142,7 +192,7 @@ class FaultTolerantJob:
             self.generations_run += 1
             failure: Optional[BaseException] = None
             try:
-                if self.generations_run > 1 or self.relaunched:
+                if self.resume:
                     import torch.distributed as dist
                     dist.barrier()
                     self.core.check_fault_tolerance(5)        # "all nodes recovered" (lr_example.cpp:266)
@@ -165,7 +215,7 @@ class MasterProcess:
     """The master node (id 1): C++ Master + heartbeat check thread, plus the rendezvous store of the
     generations (reference master/master.hpp:14-87)."""
 
-    def __init__(self, nodes, heartbeat_interval: int, relaunch_cmd: str, store_port: int):
+    def __init__(self, nodes, heartbeat_interval: int, relaunch_cmd: str, store_port: int, scale_file: str = ""):
         from .. import core
         import torch.distributed as dist
         self.core = core
@@ -176,14 +226,34 @@ class MasterProcess:
         self.store = dist.TCPStore("0.0.0.0", int(store_port), is_master=True, timeout=timedelta(seconds=120),
                                    wait_for_workers=False)
         self.store.add("generation", 0)
+        self.members: List[int] = [int(n.id) for n in self.rank_nodes]
+        self.generation = 0
+        self.store.set("members/0", ",".join(str(i) for i in self.members))
+        if scale_file:
+            core.context_set("scale_file", scale_file)
         self.master = core.Master(self.master_node, list(self.rank_nodes))
         self.rollbacks: List[int] = []
+        self.scaled: List[int] = []
+
+        def next_generation():
+            # membership first, then the counter: whoever sees the new generation finds its members
+            self.generation += 1
+            self.store.set(f"members/{self.generation}", ",".join(str(i) for i in self.members))
+            self.store.add("generation", 1)
 
         def on_rollback(failed_id: int):
             self.rollbacks.append(int(failed_id))
-            self.store.add("generation", 1)
+            next_generation()
+
+        def on_scale(node_id: int):
+            # master/master_thread.cpp:40-43: kScale -> ScaleRollBack; the new node joins the next generation
+            self.scaled.append(int(node_id))
+            if int(node_id) not in self.members:
+                self.members.append(int(node_id))
+            next_generation()
 
         self.master.set_rollback_hook(on_rollback)
+        self.master.set_scale_hook(on_scale)
 
     def serve(self):
         """Blocks until every node has said goodbye (kQuitHeartBeat)."""

@@ -5,6 +5,13 @@
   <prefix>server_progress_<id>  "min_clock:<v> <tid>:<v> ..."           (server/util/progress_tracker.hpp:68-85)
   <prefix>worker_config_<id>    "<worker_id>:<iteration> ..."           (lib/svm_dumper.hpp:51-66)
 
+  <prefix>server_layout         (this backend) JSON: node ids and the [begin, end) range behind every
+                                server_params file, written by the first node.  Restore compares it with
+                                the current partition: a cluster that grew (scale-out) or shrank since the
+                                dump re-shards while it reads, and a node that was not there at dump time
+                                takes the clock and the iteration of the others (the reference clones the
+                                progress onto the scale node's thread, progress_tracker.hpp:112-117).
+
 <id> is the node id; a node with several server shards appends ".<k>" for shards k >= 1.  Values are
 written with round-trip precision (the reference's 6 significant digits lose weights) and Restore
 parses what Dump wrote (the reference's Restore truncates to int).  Clocks / iterations are rounded
@@ -15,8 +22,9 @@ iteration (there are no server threads that could dump on a remote worker's requ
 """
 from __future__ import annotations
 
+import json
 import os
-from typing import Dict, Optional
+from typing import Dict, List, Optional
 
 import numpy as np
 import torch
@@ -122,37 +130,115 @@ def _dump_table_once(engine, table, prefix, interval, iteration_map):
     with open(_resolve(_paths(prefix, node_id, 0, "worker_config")), "w") as f:
         for w, it in sorted(it_map.items()):
             f.write(f"{w}:{round_to_interval(int(it), interval)} ")
+    if engine.rank_index == 0:
+        write_layout(prefix, table_layout(engine, table))
     engine.control.barrier()
 
 
+def table_layout(engine, table) -> dict:
+    """Which node's which file holds which keys (the partition at dump time)."""
+    node_ids = [n.id for n in engine.nodes]
+    per_node: Dict[int, int] = {}
+    shards = []
+    for s in range(table.num_shards):
+        node = node_ids[table.shard_owner[s]]
+        k = per_node.get(node, 0)
+        per_node[node] = k + 1
+        b, e = table.ranges[s]
+        shards.append({"node": int(node), "k": int(k), "begin": int(b), "end": int(e)})
+    return {"nodes": [int(i) for i in node_ids], "vals_per_key": int(table.k), "shards": shards}
+
+
+def write_layout(prefix: str, layout: dict):
+    with open(_resolve(prefix + "server_layout"), "w") as f:
+        json.dump(layout, f)
+
+
+def read_layout(prefix: str) -> Optional[dict]:
+    p = _resolve(prefix + "server_layout")
+    if not os.path.exists(p):
+        return None
+    with open(p) as f:
+        return json.load(f)
+
+
+def read_resharded(prefix: str, layout: dict, begin: int, end: int, k: int, dtype=np.float32,
+                   cache: Optional[dict] = None) -> np.ndarray:
+    """Values of keys [begin, end) collected from the dump files of a DIFFERENT partition."""
+    out = np.zeros((end - begin) * k, dtype=dtype)
+    cache = cache if cache is not None else {}
+    for sh in layout["shards"]:
+        b, e = max(begin, sh["begin"]), min(end, sh["end"])
+        if b >= e:
+            continue
+        key = (sh["node"], sh["k"])
+        if key not in cache:
+            cache[key] = read_sparse_line(_paths(prefix, sh["node"], sh["k"], "server_params"),
+                                          (sh["end"] - sh["begin"]) * k, dtype)
+        src = cache[key]
+        out[(b - begin) * k:(e - begin) * k] = src[(b - sh["begin"]) * k:(e - sh["begin"]) * k]
+    return out
+
+
+def _read_progress(prefix: str, node_id: int) -> Optional[int]:
+    p = _resolve(_paths(prefix, node_id, 0, "server_progress"))
+    if not os.path.exists(p):
+        return None
+    for tok in open(p).read().split():
+        kname, v = tok.split(":")
+        if kname == "min_clock":
+            return int(v)
+    return 0
+
+
+def _read_config(prefix: str, node_id: int) -> Optional[Dict[int, int]]:
+    p = _resolve(_paths(prefix, node_id, 0, "worker_config"))
+    if not os.path.exists(p):
+        return None
+    out: Dict[int, int] = {}
+    for tok in open(p).read().split():
+        w, it = tok.split(":")
+        out[int(w)] = int(it)
+    return out
+
+
 def restore_table(engine, table, prefix: Optional[str] = None) -> Dict[int, int]:
-    """Collective restore of a table's shards + tracker; returns the iteration map."""
+    """Collective restore of a table's shards + tracker; returns the iteration map.  The partition may
+    differ from the one that was dumped (see server_layout above)."""
     prefix = prefix if prefix is not None else str(engine.context.get("checkpoint_file_prefix", ""))
     node_id = engine.node.id
     dev = f"cuda:{table.device}"
     assert table.hview is None, "restore of hash-backed tables goes through add()"
+    np_dtype = np.float32 if table.dtype == torch.float32 else np.float64
+    layout = read_layout(prefix)
+    dumped = {(sh["node"], sh["k"], sh["begin"], sh["end"]) for sh in layout["shards"]} if layout else None
+    same_cluster = layout is None or [int(n.id) for n in engine.nodes] == layout["nodes"]
+    cache: dict = {}
     for k, s in enumerate(table.own_shards):
         b, e = table.ranges[s]
-        vals = read_sparse_line(_paths(prefix, node_id, k, "server_params"), (e - b) * table.k,
-                                np.float32 if table.dtype == torch.float32 else np.float64)
+        if dumped is None or (int(node_id), k, int(b), int(e)) in dumped:
+            vals = read_sparse_line(_paths(prefix, node_id, k, "server_params"), (e - b) * table.k, np_dtype)
+        else:
+            vals = read_resharded(prefix, layout, int(b), int(e), table.k, np_dtype, cache)
         table.shard_tensor(s).copy_(torch.from_numpy(vals).to(dev))
         table.write_epoch += 1
         if table.model_type.name == "BSP":
             table.shard_tensor(s, staging=True).zero_()
-    clock = 0
-    p = _resolve(_paths(prefix, node_id, 0, "server_progress"))
-    if os.path.exists(p):
-        for tok in open(p).read().split():
-            kname, v = tok.split(":")
-            if kname == "min_clock":
-                clock = int(v)
-    it_map: Dict[int, int] = {}
-    p = _resolve(_paths(prefix, node_id, 0, "worker_config"))
-    if os.path.exists(p):
-        for tok in open(p).read().split():
-            w, it = tok.split(":")
-            it_map[int(w)] = int(it)
+    clock = _read_progress(prefix, node_id)
+    it_map = _read_config(prefix, node_id)
+    if not same_cluster:
+        # membership changed since the dump: every node resumes from the cluster-wide minimum, and workers
+        # that did not exist then start there too (Engine.get_iteration falls back to default_iteration)
+        old = layout["nodes"]
+        clocks = [c for c in (_read_progress(prefix, n) for n in old) if c is not None]
+        clock = min(clocks) if clocks else 0
+        merged: Dict[int, int] = {}
+        for n in old:
+            merged.update(_read_config(prefix, n) or {})
+        low = min(merged.values()) if merged else 0
+        it_map = {w: low for w in merged}
+        engine.default_iteration = low
     torch.cuda.synchronize(table.device)
-    table.restored_clock = clock
+    table.restored_clock = clock or 0
     engine.control.barrier()
-    return it_map
+    return it_map or {}

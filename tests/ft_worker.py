@@ -21,8 +21,9 @@ def main():
     relaunched = "--relaunched=true" in sys.argv
     my_id, out = int(a["my_id"]), a["out_dir"]
     nodes = core.parse_file(a["config_file"])
+    scale_node = core.Node(my_id, "localhost", int(a["scale_port"])) if a.get("scale_port") else None
     job = FaultTolerantJob(nodes, my_id, a["heartbeat_interval"], a["store_port"], relaunched=relaunched,
-                           pg_timeout_s=20)
+                           pg_timeout_s=20, scale_node=scale_node, scale_file=a.get("scale_file", ""))
     job.start()
     iters, ck_every = a["num_iters"], a["checkpoint_interval"]
 
@@ -30,10 +31,17 @@ def main():
         w = torch.zeros(8, dtype=torch.float64)
         first = 0
         ck = os.path.join(out, f"ckpt_{my_id}.pt")
-        if job.resume and os.path.exists(ck):
-            st = torch.load(ck)
+        src = ck
+        if job.resume and not os.path.exists(ck):
+            # a node that scaled in has no checkpoint of its own: it takes the state of the others
+            # (the toy state is replicated; the device backend re-shards, utils/checkpoint.py)
+            others = sorted(f for f in os.listdir(out) if f.startswith("ckpt_") and f.endswith(".pt"))
+            src = os.path.join(out, others[0]) if others else ck
+        if job.resume and os.path.exists(src):
+            st = torch.load(src)
             w, first = st["w"], st["it"]
-        print(f"[node {my_id}] generation {job.generation} starts at iteration {first}", flush=True)
+        print(f"[node {my_id}] generation {job.generation} starts at iteration {first} as rank {job.rank} of "
+              f"{job.world}", flush=True)
         for it in range(first, iters):
             job.check()
             g = torch.full((8,), float((it + 1) * (job.rank + 1)), dtype=torch.float64)

@@ -263,11 +263,51 @@ def main():
 
     engine.stop_everything()
     import torch.distributed as dist
+
+    # ---- 10. elastic shrink (ForceQuit): the last rank "read no data" and leaves before the tables exist; the
+    #          survivors' tables are partitioned over the survivors only and the fused LR step still equals the
+    #          oracle of synchronous SGD over the survivors' batches
+    shrunk = 0
+    if world >= 2:
+        from minips_b200.parallel.types import Node
+        nodes10 = [Node(i, "localhost", 0) for i in range(world)]
+        e10 = Engine(nodes10[rank], nodes10, device=engine.device)
+        e10.start_everything(num_server_threads_per_node=1)
+        stay = e10.force_quit(leaving=(rank == world - 1))
+        assert stay == (rank != world - 1)
+        if stay:
+            w10 = len(e10.nodes)
+            assert w10 == world - 1 and e10.rank_index == rank
+            nd10, b10, a10 = 40_000, 4096, 0.05
+            t10 = e10.create_table(num_dims=nd10, model_type=ModelType.BSP, dtype=torch.float64)
+            assert e10.tables[t10].num_shards == w10 and e10.tables[t10].ranges[-1][1] == nd10
+            d10 = [make_synthetic(8192, nd10, 20, device=dev, seed=500 + r) for r in range(w10)]
+            d10_64 = [CsrBatchSource(d.row_ptr, d.col, d.val.double(), d.label.double()) for d in d10]
+            st10 = [torch.tensor([0, 4096, 1000]) for _ in range(w10)]
+            out10 = {}
+
+            def fn10(info):
+                tr = SparseLRTrainer(info.create_kv_client_table(t10), d10[rank], a10)
+                tr.train_dense(st10[rank].to(dev), b10)
+                out10["w"] = tr.client.get_all()
+
+            task10 = MLTask()
+            task10.set_worker_alloc([WorkerAlloc(n.id, 1) for n in e10.nodes])
+            task10.set_tables([t10])
+            task10.set_lambda(fn10)
+            e10.run(task10)
+            w_or = torch.zeros(nd10, device=dev, dtype=torch.float64)
+            for i in range(3):
+                w_or = w_or + sum(oracle_step(w_or, d10_64[r], int(st10[r][i]), b10, a10)[0] for r in range(w10))
+            torch.testing.assert_close(out10["w"], w_or, rtol=1e-9, atol=1e-12)
+            shrunk = w10
+            e10.stop_everything()
+
     if dist.is_initialized():
         dist.barrier()
         dist.destroy_process_group()
     if rank == 0:
-        print(f"MULTI_GPU_OK world={world} nvls_multicast={multicast}")
+        print(f"MULTI_GPU_OK world={world} nvls_multicast={multicast} shrunk_to={shrunk}")
 
 
 if __name__ == "__main__":

@@ -76,3 +76,54 @@ def test_kill_detect_relaunch_rollback_resume(tmp_path):
     for i in (0, 2):
         w = torch.load(out / f"final_{i}.pt")
         assert torch.allclose(w, torch.full((8,), expect, dtype=torch.float64), rtol=0, atol=1e-9), (i, w)
+
+
+def test_scale_out_new_node_joins_next_generation(tmp_path):
+    """Elastic scale-out (reference lr_example.cpp:396-409, master_thread.cpp:40-43, mailbox.cpp:197-219):
+    a job of ONE worker node is running; a new process announces itself (scale file + kScale), the master
+    adds it, publishes the membership of the next generation and broadcasts kScaleRollback; both nodes
+    meet there as ranks 0 and 1 of 2 and resume from the last checkpoint."""
+    import re
+    base = 22000 + os.getpid() % 2000
+    hostfile = tmp_path / "nodes"
+    hostfile.write_text(f"0:localhost:{base}\n1:localhost:{base + 1}\n")
+    out = tmp_path / "out"
+    out.mkdir()
+    scale_file = str(tmp_path / "scale")
+    args = {"config_file": str(hostfile), "heartbeat_interval": 1, "store_port": base + 7, "out_dir": str(out),
+            "num_iters": 120, "checkpoint_interval": 20, "iter_sleep": 0.2, "scale_file": scale_file}
+    worker = os.path.join(ROOT, "tests", "ft_worker.py")
+    env = dict(os.environ, MINIPS_LOG="0")
+    master = subprocess.Popen(
+        [sys.executable, "-m", "minips_b200.apps.master", f"--config_file={hostfile}", "--heartbeat_interval=1",
+         f"--store_port={base + 7}", f"--scale_file={scale_file}"], cwd=ROOT, env=env, stdout=subprocess.PIPE,
+        stderr=subprocess.STDOUT, text=True)
+    time.sleep(1.0)
+    procs = {0: subprocess.Popen([sys.executable, worker, json.dumps(dict(args, my_id=0))], cwd=ROOT, env=env,
+                                 stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True)}
+    try:
+        assert _wait_for(out / "progress_0", lambda s: int(s) >= 25, 60), "node 0 never reached iteration 25"
+        procs[2] = subprocess.Popen([sys.executable, worker, json.dumps(dict(args, my_id=2, scale_port=base + 2))],
+                                    cwd=ROOT, env=env, stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True)
+        outs = {}
+        for i, p in procs.items():
+            outs[i], _ = p.communicate(timeout=120)
+            assert p.returncode == 0, outs[i]
+        mout, _ = master.communicate(timeout=60)
+        assert master.returncode == 0, mout
+    finally:
+        for p in list(procs.values()) + [master]:
+            if p.poll() is None:
+                p.kill()
+    assert "scale-outs for [2]" in mout, mout
+    assert open(scale_file).read().strip() == f"2:localhost:{base + 2}"
+    m0 = re.search(r"generation 1 starts at iteration (\d+) as rank 0 of 2", outs[0])
+    m2 = re.search(r"generation 1 starts at iteration (\d+) as rank 1 of 2", outs[2])
+    assert m0 and m2 and m0.group(1) == m2.group(1), (outs[0], outs[2])
+    c = int(m0.group(1))
+    assert c >= 20 and c % 20 == 0
+    # one node up to the checkpoint, two nodes after it: w = 1e-3 (sum_{it<c} (it+1) + 3 sum_{it>=c} (it+1))
+    expect = 1e-3 * (sum(range(1, c + 1)) + 3 * sum(range(c + 1, 121)))
+    for i in (0, 2):
+        w = torch.load(out / f"final_{i}.pt")
+        assert torch.allclose(w, torch.full((8,), expect, dtype=torch.float64), rtol=0, atol=1e-9), (i, w, expect)
