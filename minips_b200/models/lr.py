@@ -234,7 +234,9 @@ class SparseLRTrainer:
 
         protocol: "xchg" = reduce at the owner, owner broadcasts (BSP, one worker per rank);
         "pushpull" = slab pull / slab push per iteration (any consistency model); "auto" picks
-        xchg whenever it applies.  Between two xchg launches on a table the OTHER ranks must not
+        xchg whenever it applies (every rank then has to make the same sequence of calls with the same
+        number of iterations each: the kernel counts its hand-overs per launch).  Between two xchg launches
+        on a table the OTHER ranks must not
         Add through the generic path (this rank's own generic writes are noticed and the replica
         is refreshed)."""
         c = self.client

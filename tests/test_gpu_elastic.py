@@ -56,7 +56,10 @@ def test_scale_out_resharded_resume_equals_two_rank_run(tmp_path):
             if f.startswith("ck_"):
                 shutil.copy(d / f, snap / f)
         procs[2] = subprocess.Popen(
-            app + COMMON + ft + ["--my_id=2", "--scale=true", "--scale_name=localhost", f"--scale_port={base + 2}"],
+            # the same flags as rank 0 (the pause only acts in a first generation): every rank must cut the run
+            # into the same launches, the exchange kernel counts its hand-overs per launch
+            app + COMMON + ft + ["--my_id=2", "--scale=true", "--scale_name=localhost", f"--scale_port={base + 2}",
+                                 "--pause_at_iter=150", "--pause_s=150"],
             cwd=ROOT, env=dict(env, LOCAL_RANK="1"), stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True)
         for i, p in procs.items():
             outs[i], _ = p.communicate(timeout=300)
