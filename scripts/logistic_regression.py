@@ -1,6 +1,7 @@
 #!/usr/bin/env python3
 """LRExample launcher (reference scripts/logistic_regression.py:17-93).
-   scripts/logistic_regression.py [local | gpu [N] | relaunch <id> | scale <id> <host> <port> | kill]"""
+   scripts/logistic_regression.py [local | relaunch <id> | scale <id> <host> <port> | kill]      host runtime
+   scripts/logistic_regression.py [gpu [N] | gpuft | gpuscale <id> <host> <port> <cuda> | gpurelaunch <id>]   device"""
 import os
 import sys
 
@@ -38,7 +39,7 @@ params = {
     "assigner_master_port": 19201,
     "block_size": 65536,
 }
-if len(sys.argv) > 1 and sys.argv[1] == "gpu":
+if len(sys.argv) > 1 and sys.argv[1] in ("gpu", "gpuft", "gpuscale", "gpurelaunch"):
     params.update({"num_dims": 1000000, "batch_size": 65536, "num_samples": 2000000, "kModelType": "BSP",
                    "num_workers_per_node": 1, "checkpoint_toggle": "false"})
 

@@ -43,3 +43,25 @@ def test_restore_reshards_when_the_partition_changed(tmp_path):
             got = ck.read_resharded(prefix, layout, b, e, 2, np.float64, cache)
             np.testing.assert_array_equal(got, full[2 * b:2 * e])
     assert ck.read_layout(str(tmp_path / "nothing_")) is None
+
+
+def test_launcher_builds_fault_tolerant_and_scale_out_commands(tmp_path):
+    sys.path.insert(0, os.path.join(ROOT, "scripts"))
+    import launch_utils as lu
+    hostfile = tmp_path / "nodes"
+    hostfile.write_text("0:localhost:9000\n1:localhost:9001\n2:localhost:9002\n")
+    params = {"num_dims": 1000, "heartbeat_interval": -1, "relaunch_cmd": "x y"}
+    cmds = lu.gpu_ft_commands("minips_b200.apps.lr_example", str(hostfile), params, store_port=29701,
+                              scale_file="/tmp/s")
+    assert len(cmds) == 3
+    env0, master = cmds[0]
+    assert "minips_b200.apps.master" in master and "--heartbeat_interval=1" in master and "--relaunch_cmd=x y" in master
+    (e1, r1), (e2, r2) = cmds[1], cmds[2]
+    assert e1 == {"LOCAL_RANK": "0"} and "--my_id=0" in r1 and "--store_port=29701" in r1
+    assert e2 == {"LOCAL_RANK": "1"} and "--my_id=2" in r2 and not any(a.startswith("--relaunch_cmd") for a in r2)
+    env, cmd = lu.gpu_scale_command("minips_b200.apps.lr_example", str(hostfile), params, 7, "hostb", 9100, 3)
+    assert env == {"LOCAL_RANK": "3"}
+    for a in ("--my_id=7", "--scale=true", "--scale_name=hostb", "--scale_port=9100", "--heartbeat_interval=1"):
+        assert a in cmd, (a, cmd)
+    env, cmd = lu.gpu_relaunch_command("minips_b200.apps.lr_example", str(hostfile), params, 2)
+    assert env == {"LOCAL_RANK": "1"} and "--use_weight_file=true" in cmd and "--relaunched=true" in cmd
