@@ -10,6 +10,7 @@
 //
 //   build/bin/lr_example --my_id=0 --config_file=config/localnodes --input=/tmp/a.libsvm \
 //       --num_dims=1000 --kModelType=BSP --batch_size=100 --num_iters=100 --heartbeat_interval=-1
+#include <atomic>
 #include <chrono>
 #include <cmath>
 #include <iostream>
@@ -144,6 +145,7 @@ static int Training(const Node& my_node, const std::vector<Node>& nodes, const N
   task.SetWorkerAlloc(alloc);
   task.SetTables({table});
   std::mutex print_mu;
+  std::atomic<bool> recovered_logged{false};
   task.SetLambda([&](const Info& info) {
     lib::BatchDataSampler<SVMItem> sampler(data, batch,
         static_cast<uint64_t>(ctx.get_int32("seed")) * 1000 + info.worker_id + 1);
@@ -168,6 +170,8 @@ static int Training(const Node& my_node, const std::vector<Node>& nodes, const N
         continue;
       }
       t->Get(keys, &params);
+      // the first Get of a relaunched node was answered: every node is back (lr_example.cpp:265-268)
+      if (resume && !recovered_logged.exchange(true)) CheckFaultTolerance(5);
       if (engine.IsNeedRollBack()) {  // lr_example.cpp:265-288
         if (engine.IncRollBackCount() == 1) {
           engine.Barrier();  // meets the restarted node's fault barrier
