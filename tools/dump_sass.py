@@ -24,7 +24,9 @@ HOT = [
     r"kmeans_assign_tc_kernel<1>", r"kmeans_sorted_sum_kernel<128>", r"kmeans_delta_push_kernel",
     r"dense_lr_forward_kernel", r"dense_lr_grad_kernel", r"pull_dense_f32_kernel", r"push_dense_f32_kernel",
     r"pull_kernel<float>", r"push_kernel<float>", r"clock_kernel", r"csr_unpack_kernel", r"parse_lines_kernel",
-    r"hash_add_kernel", r"hash_get_kernel",
+    r"hash_add_kernel", r"hash_get_kernel", r"dense_lr_rows_kernel", r"dense_lr_stream_kernel",
+    r"dense_lr_fused_kernel", r"lr_step_bucket_kernel<8, float>", r"lr_step_bucket_kernel<8, double>",
+    r"fold_server_kernel",
 ]
 
 
