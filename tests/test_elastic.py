@@ -12,7 +12,7 @@ ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 
 
 def test_force_quit_shrinks_cluster():
-    port = 21000 + os.getpid() % 2000
+    port = 31000 + os.getpid() % 1000
     p = subprocess.run([sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node=3",
                         "--master-addr=127.0.0.1", f"--master-port={port}",
                         os.path.join(ROOT, "tests", "elastic_worker.py")],

@@ -24,7 +24,7 @@ COMMON = ["--kModelType=BSP", "--dtype=fp64", "--num_dims=20000", "--num_samples
 def test_scale_out_resharded_resume_equals_two_rank_run(tmp_path):
     if torch.cuda.device_count() < 2:
         pytest.skip("needs >= 2 GPUs")
-    base = 24000 + os.getpid() % 2000
+    base = 28000 + os.getpid() % 1400
     d = tmp_path / "elastic"
     d.mkdir()
     hostfile = d / "nodes"

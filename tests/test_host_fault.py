@@ -23,7 +23,7 @@ def _progress(path):
 
 
 def test_host_kill_detect_relaunch_rollback(built, dataset, tmp_path):  # noqa: F811
-    base = 23000 + os.getpid() % 2000
+    base = 29000 + os.getpid() % 480
     d = str(tmp_path)
     hostfile = tmp_path / "nodes"
     hostfile.write_text("".join(f"{i}:localhost:{base + i}\n" for i in range(3)))
