@@ -9,11 +9,12 @@ pytestmark = pytest.mark.gpu
 
 
 @pytest.mark.parametrize("mode", ["rows", "stream", "mma", "twopass"])
-@pytest.mark.parametrize("n,D", [(4096, 512), (10_007, 1000), (300, 64), (2048, 4096)])
+@pytest.mark.parametrize("n,D", [(4096, 512), (10_007, 1000), (300, 64), (2048, 4096), (3001, 1024), (29, 8)])
 def test_dense_lr_training_matches_oracle(n, D, mode, monkeypatch):
-    """Three implementations of the iteration against the same oracle: "stream" (TMA-fed, X read once, the
-    default), "mma" (both products on tcgen05, the second one with the tile as an MN-major operand) and
-    "twopass" (tcgen05 forward + CUDA-core gradient pass; also what D > 1024 takes)."""
+    """Four implementations of the iteration against the same oracle: "rows" (warp per row, bulk-copy ring,
+    nothing resident; the default), "stream" (TMA-fed, 64-row tile resident), "mma" (both products on tcgen05,
+    the second one with the tile as an MN-major operand) and "twopass" (tcgen05 forward + CUDA-core gradient
+    pass; also what D > 1024 takes)."""
     monkeypatch.setenv("MINIPS_DENSE_LR", mode)
     from minips_b200.models.dense_lr import DenseLRTrainer, oracle_step
     from minips_b200.parallel.engine import Engine
