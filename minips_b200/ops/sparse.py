@@ -4,7 +4,7 @@ the per-batch sorted unique key set (lib/batch_data_sampler.cpp:50-71) and libsv
 from __future__ import annotations
 
 import ctypes as C
-from typing import Optional, Tuple
+from typing import Optional
 
 import torch
 

@@ -10,7 +10,6 @@ from __future__ import annotations
 
 import os
 import threading
-import time
 from dataclasses import dataclass
 from typing import Callable, Dict, List, Optional, Sequence
 

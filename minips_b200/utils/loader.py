@@ -8,7 +8,7 @@ training kernel of batch i runs; an event hands the staged buffers to the comput
 from __future__ import annotations
 
 import os
-from typing import List, Optional, Tuple
+from typing import Optional
 
 import torch
 
