@@ -17,4 +17,5 @@ want lr_xchg_fp64 && cap lr_xchg_fp64 lr_train_xchg 1 python tools/profile_lr.py
 want lr_xchg_fp32 && cap lr_xchg_fp32 lr_train_xchg 1 python tools/profile_lr.py --ncu --dtype fp32
 want kmeans_assign && cap kmeans_assign kmeans_assign_tc 1 python tools/profile_kmeans.py --ncu
 want dense_lr_rows && cap dense_lr_rows dense_lr_rows_kernel 1 python tools/profile_dense_lr.py --iters 2
+want dense_lr_mma && MINIPS_DENSE_LR=mma cap dense_lr_mma dense_lr_fused_kernel 1 python tools/profile_dense_lr.py --iters 2
 ls -la $O
