@@ -36,6 +36,8 @@
 //
 // Requires: BSP, every rank of the table runs exactly one worker through this kernel with the
 // same n_iters and the same grid size, one value per key.
+#include <mutex>
+
 #include "lr_common.cuh"
 
 namespace mps {
@@ -277,14 +279,33 @@ static int launch_xchg(const MpsTableView* view, const MpsClockView* clk, int wo
                        const MpsCsr* csr, const int64_t* batch_starts, int n_iters, int64_t batch, double alpha_f,
                        const MpsXchg* xchg, float* loss_out, unsigned long long* timeline, int avg_nnz,
                        int max_ctas, cudaStream_t st) {
-  int dev = 0, sms = 148, per_sm = 0;
-  cudaGetDevice(&dev);
-  cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
   const int L = lanes_for(avg_nnz > 0 ? avg_nnz : 40);
   void* fn = csr->format == MPS_CSR_PACKED ? xchg_kernel_for<T, true>(L) : xchg_kernel_for<T, false>(L);
-  MPS_CHECK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, fn, 512, 0));
-  if (per_sm < 1) return static_cast<int>(cudaErrorLaunchOutOfResources);
-  int grid = sms * per_sm;
+  // the co-resident grid of a kernel variant never changes: asked once per variant and process (every launch
+  // is inside somebody's timed region, and the two runtime queries cost more host time than the launch)
+  static void* cached_fn[12];
+  static int cached_grid[12];
+  static std::mutex cache_mu;
+  int grid = 0;
+  {
+    std::lock_guard<std::mutex> lk(cache_mu);
+    int slot = 0;
+    while (slot < 12 && cached_fn[slot] != nullptr && cached_fn[slot] != fn) ++slot;
+    if (slot < 12 && cached_fn[slot] == fn) {
+      grid = cached_grid[slot];
+    } else {
+      int dev = 0, sms = 148, per_sm = 0;
+      cudaGetDevice(&dev);
+      cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+      MPS_CHECK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, fn, 512, 0));
+      if (per_sm < 1) return static_cast<int>(cudaErrorLaunchOutOfResources);
+      grid = sms * per_sm;
+      if (slot < 12) {
+        cached_fn[slot] = fn;
+        cached_grid[slot] = grid;
+      }
+    }
+  }
   if (max_ctas > 0 && grid > max_ctas) grid = max_ctas;
   MpsTableView v = *view;
   MpsClockView c = *clk;
