@@ -119,8 +119,8 @@ def measure_lr(engine, args, data, dtype_name, want_e2e, want_timeline=False):
                 tr.step_sparse(s, B, out[i])
             return out
 
+        sampler = ClockSampler(engine.device).start()         # samples through warm-up and every timed region
         run(starts(W))                                       # warm-up (untimed)
-        sampler = ClockSampler(engine.device).start()
         times, loss = [], None
         for _ in range(R):
             st = starts(K)

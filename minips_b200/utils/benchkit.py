@@ -43,6 +43,11 @@ class ClockSampler:
         self.proc = subprocess.Popen(
             [exe, f"--id={idx}", f"--query-gpu={_Q}", "--format=csv,noheader,nounits", "-lms", str(self.period_ms)],
             stdout=self._out, stderr=subprocess.DEVNULL)
+        # nvidia-smi needs a few hundred ms to come up (NVML init); wait for its first line so that its start-up
+        # does not land inside the first timed region
+        end = time.time() + 2.0
+        while time.time() < end and os.path.getsize(self.path) == 0 and self.proc.poll() is None:
+            time.sleep(0.02)
         return self
 
     def stop(self) -> Dict:
